@@ -1,0 +1,511 @@
+// pic_device.cuh -- device code of the B200-native PIC-MCC electron engine (sm_100a).
+//
+// Everything here is written from scratch for Blackwell; the reference lines cited are the
+// *semantics* each kernel reproduces (paths relative to MagnusMouritzen/particle-simulation).
+//
+// Data layout in HBM: structure-of-arrays, fp32 state, one array per field, each `capacity`
+// long and 256-byte aligned:  x y z | vx vy vz | ax ay az | ts (int32) | id (uint64).
+// 48 B per electron, of which a mobility step must move 68 B (read 40, write 28; the id is
+// bookkeeping the reference does not have).  The charge grid is 512^3 int32 (512 MiB), kept
+// all-zero outside the bounding box of the last deposit, so no pass ever sweeps it whole.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace picb200 {
+
+constexpr int kGrid = 512;              // src/cell.cu:3
+constexpr int kRows = 10000;            // src/cross_section.h:9
+constexpr int kDead = -2;               // src/electron.h:8
+constexpr unsigned kFull = 0xffffffffu;
+constexpr uint32_t kTagCollide = 0u, kTagInit = 1u;
+
+// Shared-memory image of the collision tables: kRows x {split, split+remove} then
+// kRows+1 bin-edge energies (see build_energy_edges() in pic_engine.cu).
+constexpr int kThrBytes = kRows * 8;
+constexpr int kEdgeBytes = (kRows + 1) * 4;
+constexpr int kTableSmemBytes = ((kThrBytes + kEdgeBytes + 15) / 16) * 16;
+
+struct Soa {
+    float *x, *y, *z, *vx, *vy, *vz, *ax, *ay, *az;
+    int* ts;
+    unsigned long long* id;
+};
+
+// Device-resident control block.  Every kernel sizes itself from here, so a whole Poisson
+// step (or a whole run) is enqueued without the host ever reading a counter back
+// (contrast src/pic.cu:495-497, :539, :551: three blocking copies per Poisson step).
+struct DevState {
+    int n;                  // live electrons = slots [0,n); all ts == -1 between Poisson steps
+    int n_alloc;            // append cursor during the mobility phase (may overshoot capacity)
+    int n_dead;             // electrons marked DEAD in this Poisson step
+    int n_holes, n_movers;  // compaction work lists
+    unsigned bar_count, bar_release;   // grid barrier of the persistent mover
+    int gen_hi;             // generation window end agreed at the barrier
+    int bbox_lo[3], bbox_hi[3];        // cell bounding box of the charge currently deposited
+    int poisson_index;      // Poisson steps completed
+    int hit_zero;           // population reached 0 (src/pic.cu:556-559)
+    int overflow_steps;     // steps whose n reached capacity (src/pic.cu:544)
+    int last_n_after_mobility;
+    unsigned long long pushes;         // updateParticle evaluations
+    long long total_added, total_removed;
+};
+
+struct StepLog { int n_after_mobility, n_after_compaction; };
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ int ld_volatile_i32(const int* p) { return *(const volatile int*)p; }
+
+// Philox4x32-10 (Salmon et al. SC'11).  Replaces the per-slot XORWOW state of
+// src/random.cu:3-12: no state array, keyed on (seed, particle id, step block).
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+    constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+        uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += W0;
+        k.y += W1;
+    }
+    return c;
+}
+// curand_uniform's (0,1] mapping used by randFloat (src/random.cu:7-12).
+__device__ __forceinline__ float uniform01(uint32_t w) {
+    return __fmaf_rn(__uint2float_rn(w), 0x1p-32f, 0x1p-33f);
+}
+// Identity of a child spawned by `parent` at global mobility step g (splitmix64 finaliser).
+__device__ __forceinline__ unsigned long long child_id(unsigned long long parent, unsigned long long g) {
+    unsigned long long z = parent + g * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= (z >> 31);
+    return z | 0x8000000000000000ull;
+}
+
+// energyToIndex (src/cross_section.cu:32-35) without the fp64 log10: a cubic estimate of
+// s = (log10(E)+6)*10000/22 (|error| < 0.15), rounded to the nearest bin boundary j, then one
+// shared-memory probe of the exact boundary energy: edge[j] is the smallest fp32 E whose
+// reference index (double formula) is >= j.  The result equals the reference formula for every
+// fp32 E (verified exhaustively on the CPU by tests/tools/check_energy_index.cpp).
+__device__ __forceinline__ int energy_index(float e, const float* __restrict__ s_edge) {
+    const uint32_t b = __float_as_uint(e);
+    const int ex = (int)(b >> 23) - 127;
+    const float m = __uint_as_float((b & 0x007fffffu) | 0x3f800000u);
+    float p = __fmaf_rn(m, 0.155445858836174f, -1.0392581224441528f);
+    p = __fmaf_rn(p, m, 3.0294783115386963f);
+    p = __fmaf_rn(p, m, -2.1449406147003174f);
+    const float lg = __int2float_rn(ex) + p;                                   // ~log2(E)
+    const float s = __fmaf_rn(lg, 136.83181621090054f, 2727.2727272727275f);   // *log10(2)*1e4/22, +6e4/22
+    int j = __float2int_rn(s);
+    j = max(0, min(j, kRows));
+    int idx = j - ((e < s_edge[j]) ? 1 : 0);
+    idx = min(idx, kRows - 1);
+    return (e != e) ? 0 : idx;      // NaN: the reference's saturating cvt gives 0
+}
+
+// cell index of a coordinate: int(pos / cell_size), double divide, C truncation
+// (src/grid_operations.cu:21-23, :65-67), clamped for memory safety.
+__device__ __forceinline__ int cell_of(float p) {
+    int c = __double2int_rz((double)p / 1e-2);
+    return max(0, min(c, kGrid - 1));
+}
+__device__ __forceinline__ size_t cell_index(int ix, int iy, int iz) {
+    return ((size_t)iz * kGrid + (size_t)iy) * kGrid + (size_t)ix;
+}
+
+// ------------------------------------------------------------------------------------------
+// K_init: setup_particles (src/particle_move.cu:7-19).  Three Philox words -> x,y,z in
+// (2.26, 2.88]; velocity and acceleration start at 0 (uninitialised in the reference).
+// ------------------------------------------------------------------------------------------
+__global__ void k_init_uniform(Soa s, DevState* st, int init_n, unsigned long long id_base, uint2 seed) {
+    const float lo = (float)((kGrid / 2 - 30) * 1e-2);
+    const float hi = (float)((kGrid / 2 + 32) * 1e-2);
+    const float range = __fsub_rn(hi, lo);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < init_n; i += gridDim.x * blockDim.x) {
+        unsigned long long id = id_base + (unsigned long long)i;
+        uint4 r = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), 0u, kTagInit), seed);
+        s.x[i] = __fmaf_rn(uniform01(r.x), range, lo);
+        s.y[i] = __fmaf_rn(uniform01(r.y), range, lo);
+        s.z[i] = __fmaf_rn(uniform01(r.z), range, lo);
+        s.vx[i] = 0.f; s.vy[i] = 0.f; s.vz[i] = 0.f;
+        s.ax[i] = 0.f; s.ay[i] = 0.f; s.az[i] = 0.f;
+        s.ts[i] = -1;
+        s.id[i] = id;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { st->n = init_n; st->n_alloc = init_n; }
+}
+
+// ------------------------------------------------------------------------------------------
+// K_deposit: particlesToGrid (src/grid_operations.cu:15-26).  Nearest-grid-point count with
+// warp-level pre-reduction (__match_any_sync groups lanes that hit the same cell; one
+// red.global.add per group) and a block-reduced cell bounding box.
+// ------------------------------------------------------------------------------------------
+__global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge) {
+    __shared__ int s_lo[3], s_hi[3];
+    if (threadIdx.x < 3) { s_lo[threadIdx.x] = kGrid; s_hi[threadIdx.x] = -1; }
+    __syncthreads();
+    const int n = st->n;
+    const int lane = threadIdx.x & 31;
+    const int rounded = (n + 31) & ~31;
+    int lx = kGrid, ly = kGrid, lz = kGrid, hx = -1, hy = -1, hz = -1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        const bool in = i < n;
+        unsigned cell = 0xffffffffu - (unsigned)lane;          // unique per lane when inactive
+        if (in) {
+            int ix = cell_of(__ldcg(s.x + i)), iy = cell_of(__ldcg(s.y + i)), iz = cell_of(__ldcg(s.z + i));
+            cell = (unsigned)cell_index(ix, iy, iz);
+            lx = min(lx, ix); ly = min(ly, iy); lz = min(lz, iz);
+            hx = max(hx, ix); hy = max(hy, iy); hz = max(hz, iz);
+        }
+        const unsigned peers = __match_any_sync(kFull, cell);
+        if (in && lane == __ffs(peers) - 1) atomicAdd(charge + cell, __popc(peers));
+    }
+    lx = __reduce_min_sync(kFull, lx); ly = __reduce_min_sync(kFull, ly); lz = __reduce_min_sync(kFull, lz);
+    hx = __reduce_max_sync(kFull, hx); hy = __reduce_max_sync(kFull, hy); hz = __reduce_max_sync(kFull, hz);
+    if (lane == 0 && hx >= 0) {
+        atomicMin(&s_lo[0], lx); atomicMin(&s_lo[1], ly); atomicMin(&s_lo[2], lz);
+        atomicMax(&s_hi[0], hx); atomicMax(&s_hi[1], hy); atomicMax(&s_hi[2], hz);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 && s_hi[threadIdx.x] >= 0) {
+        atomicMin(&st->bbox_lo[threadIdx.x], s_lo[threadIdx.x]);
+        atomicMax(&st->bbox_hi[threadIdx.x], s_hi[threadIdx.x]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K_gather: updateGrid + gridToParticles fused (src/grid_operations.cu:29-72).  Each electron
+// differences the six neighbour counts of its own cell: acc = float(EFC * double(c+ - c-)),
+// absent neighbours at the domain faces count as 0.  Bit-identical to computing the per-cell
+// field first, without the 12 B/cell field array or any whole-grid pass.
+// ------------------------------------------------------------------------------------------
+__global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ charge, double efc) {
+    const int n = st->n;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int ix = cell_of(__ldcg(s.x + i)), iy = cell_of(__ldcg(s.y + i)), iz = cell_of(__ldcg(s.z + i));
+        const int* c = charge + cell_index(ix, iy, iz);
+        const int xm = (ix != 0) ? __ldg(c - 1) : 0;
+        const int xp = (ix != kGrid - 1) ? __ldg(c + 1) : 0;
+        const int ym = (iy != 0) ? __ldg(c - kGrid) : 0;
+        const int yp = (iy != kGrid - 1) ? __ldg(c + kGrid) : 0;
+        const int zm = (iz != 0) ? __ldg(c - kGrid * kGrid) : 0;
+        const int zp = (iz != kGrid - 1) ? __ldg(c + kGrid * kGrid) : 0;
+        __stcg(s.ax + i, __double2float_rn(__dmul_rn(efc, (double)(xp - xm))));
+        __stcg(s.ay + i, __double2float_rn(__dmul_rn(efc, (double)(yp - ym))));
+        __stcg(s.az + i, __double2float_rn(__dmul_rn(efc, (double)(zp - zm))));
+    }
+}
+
+// K_clear: resetGrid (src/grid_operations.cu:6-12) restricted to the deposited bounding box.
+__global__ void k_clear_box(const DevState* st, int* __restrict__ charge) {
+    const int lx = st->bbox_lo[0], ly = st->bbox_lo[1], lz = st->bbox_lo[2];
+    const int wx = st->bbox_hi[0] - lx + 1, wy = st->bbox_hi[1] - ly + 1, wz = st->bbox_hi[2] - lz + 1;
+    if (wx <= 0 || wy <= 0 || wz <= 0) return;
+    const long long total = (long long)wx * wy * wz;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
+        const int x = (int)(k % wx);
+        const long long r = k / wx;
+        const int y = (int)(r % wy), z = (int)(r / wy);
+        charge[cell_index(lx + x, ly + y, lz + z)] = 0;
+    }
+}
+__global__ void k_set_n(DevState* st, int n) { st->n = n; st->n_alloc = n; }
+__global__ void k_reset_bbox(DevState* st) {
+    if (threadIdx.x < 3) { st->bbox_lo[threadIdx.x] = kGrid; st->bbox_hi[threadIdx.x] = -1; }
+}
+
+// Multi-GPU: the union bounding box is one max-reduction of {-lo[3], hi[3], 0, 0}.
+__global__ void k_bbox_encode(const DevState* st, int* red) {
+    if (threadIdx.x < 3) { red[threadIdx.x] = -st->bbox_lo[threadIdx.x]; red[3 + threadIdx.x] = st->bbox_hi[threadIdx.x]; }
+    if (threadIdx.x >= 6 && threadIdx.x < 8) red[threadIdx.x] = 0;
+}
+__global__ void k_bbox_decode(DevState* st, const int* red) {
+    if (threadIdx.x < 3) { st->bbox_lo[threadIdx.x] = -red[threadIdx.x]; st->bbox_hi[threadIdx.x] = red[3 + threadIdx.x]; }
+}
+
+// pack / unpack the charge box into a contiguous buffer for the multi-GPU all-reduce
+__global__ void k_pack_box(const int* __restrict__ charge, int* __restrict__ buf, int lx, int ly, int lz, int wx, int wy, int wz, int unpack) {
+    const long long total = (long long)wx * wy * wz;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
+        const int x = (int)(k % wx);
+        const long long r = k / wx;
+        const int y = (int)(r % wy), z = (int)(r / wy);
+        int* g = const_cast<int*>(charge) + cell_index(lx + x, ly + y, lz + z);
+        if (unpack) *g = buf[k]; else buf[k] = *g;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K_mover: leapfrog + bounds + Monte-Carlo collision (updateParticle, src/particle_move.cu:22-87)
+// under the three scheduling disciplines of src/pic.cu:
+//   kPersistent = true : modes 30/33 -- one cooperative launch per Poisson step; electrons stay
+//       in registers for all remaining mobility steps; children are appended with one
+//       warp-aggregated atomic and consumed generation by generation inside the same launch
+//       (a device-side queue window [lo,hi) advanced at a grid barrier) -- no host round trip.
+//   kPersistent = false: mode 31 (host passes the window of one generation) and mode 32
+//       (host passes t_from == t_to, one mobility step per launch).
+// ------------------------------------------------------------------------------------------
+struct MoverArgs {
+    Soa s;
+    DevState* st;
+    const float* tables;   // global image of the shared-memory tables (kTableSmemBytes)
+    int capacity, pt;
+    int lo, hi, t_from, t_to;   // kPersistent == false only
+    uint2 seed;
+};
+
+__device__ __forceinline__ int mover_barrier_next_window(DevState* st, unsigned gen, int capacity) {
+    __shared__ int s_hi;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned target = (gen + 1u) * gridDim.x;
+        const unsigned prev = atomicAdd(&st->bar_count, 1u);
+        if (prev + 1u == target) {           // last block to arrive fixes the next window
+            __threadfence();
+            st->gen_hi = min(ld_volatile_i32(&st->n_alloc), capacity);
+            __threadfence();
+            atomicExch(&st->bar_release, gen + 1u);
+        } else {
+            while (ld_acquire_u32(&st->bar_release) < gen + 1u) __nanosleep(64);
+        }
+        __threadfence();
+        s_hi = ld_volatile_i32(&st->gen_hi);
+    }
+    __syncthreads();
+    return s_hi;
+}
+
+template <bool kPersistent>
+__global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const float2* s_thr = reinterpret_cast<const float2*>(smem_raw);
+    const float* s_edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
+    {   // stage the collision tables (120 KB) once per CTA, 128-bit copies
+        const float4* src = reinterpret_cast<const float4*>(a.tables);
+        float4* dst = reinterpret_cast<float4*>(smem_raw);
+        for (int k = threadIdx.x; k < kTableSmemBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
+    }
+    __syncthreads();
+
+    DevState* st = a.st;
+    const Soa s = a.s;
+    const int cap = a.capacity, pt = a.pt;
+    const unsigned g0 = (unsigned)st->poisson_index * (unsigned)pt;
+    const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
+    const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
+    const int lane = threadIdx.x & 31;
+    int lo, hi, t_from, t_to;
+    if (kPersistent) { lo = 0; hi = min(st->n, cap); t_from = 1; t_to = pt; }
+    else { lo = a.lo; hi = a.hi; t_from = a.t_from; t_to = a.t_to; }
+
+    unsigned long long my_pushes = 0;
+    int my_dead = 0;
+    unsigned gen = 0;
+    for (;;) {
+        const int span = hi - lo;
+        const int rounded = (span + 31) & ~31;
+        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += gridDim.x * blockDim.x) {
+            const int i = lo + k;
+            const bool in = k < span;
+            float x = 0, y = 0, z = 0, vx = 0, vy = 0, vz = 0, ax = 0, ay = 0, az = 0;
+            int ts = kDead;
+            unsigned long long id = 0;
+            if (in) {
+                x = __ldcg(s.x + i); y = __ldcg(s.y + i); z = __ldcg(s.z + i);
+                vx = __ldcg(s.vx + i); vy = __ldcg(s.vy + i); vz = __ldcg(s.vz + i);
+                ax = __ldcg(s.ax + i); ay = __ldcg(s.ay + i); az = __ldcg(s.az + i);
+                ts = __ldcg(s.ts + i);
+                id = __ldcg(s.id + i);
+            }
+            const int ts0 = ts;
+            bool alive = in && ts != kDead;
+            // first step of this electron: max(1, timestamp+1)  (src/pic.cu:218)
+            const int t0 = alive ? max(t_from, max(1, ts + 1)) : 0x7fffffff;
+            const int t_begin = __reduce_min_sync(kFull, t0);
+            bool touched = false;
+            uint4 rnd = make_uint4(0, 0, 0, 0);
+            unsigned cur_blk = 0xffffffffu;
+            for (int t = t_begin; t <= t_to; ++t) {
+                bool spawn = false;
+                float cvx = 0, cvy = 0, cvz = 0;
+                const unsigned g = g0 + (unsigned)t;
+                if (alive && t >= t0) {
+                    touched = true;
+                    ++my_pushes;
+                    // leapfrog, src/particle_move.cu:22-39
+                    vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
+                    x = __fmaf_rn(vx, dt, x); y = __fmaf_rn(vy, dt, y); z = __fmaf_rn(vz, dt, z);
+                    vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
+                    // checkOutOfBounds, src/particle_move.cu:41-52 (no draw consumed)
+                    if (x < 0.f || x >= sim || y < 0.f || y >= sim || z < 0.f || z >= sim) {
+                        alive = false; ts = kDead; ++my_dead;
+                    } else {
+                        // collider, src/particle_move.cu:55-80
+                        const unsigned blk = g >> 2;
+                        if (blk != cur_blk) {
+                            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), blk, kTagCollide), a.seed);
+                            cur_blk = blk;
+                        }
+                        const unsigned sel = g & 3u;
+                        const uint32_t w = sel == 0 ? rnd.x : (sel == 1 ? rnd.y : (sel == 2 ? rnd.z : rnd.w));
+                        const float r = __fmul_rn(uniform01(w), 100.0f);
+                        const float e = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
+                        const float2 th = s_thr[energy_index(e, s_edge)];
+                        if (r < th.x) {              // ionisation: child copies the pre-flip state
+                            spawn = true;
+                            cvx = vx; cvy = vy; cvz = vz;
+                            vx = -vx; vy = -vy; vz = -vz;
+                        } else if (r < th.y) {       // attachment: electron removed
+                            alive = false; ts = kDead; ++my_dead;
+                        }
+                    }
+                }
+                // warp-aggregated append into [n_alloc, capacity)  (cf. src/pic.cu:219-229, :276-287)
+                const unsigned m = __ballot_sync(kFull, spawn);
+                if (m) {
+                    const int leader = __ffs(m) - 1;
+                    int base = 0;
+                    if (lane == leader) {
+                        base = (ld_volatile_i32(&st->n_alloc) < cap) ? atomicAdd(&st->n_alloc, __popc(m)) : cap;
+                    }
+                    base = __shfl_sync(kFull, base, leader);
+                    if (spawn) {
+                        const int slot = base + __popc(m & lanemask_lt());
+                        if (slot < cap) {
+                            __stcg(s.x + slot, x); __stcg(s.y + slot, y); __stcg(s.z + slot, z);
+                            __stcg(s.vx + slot, cvx); __stcg(s.vy + slot, cvy); __stcg(s.vz + slot, cvz);
+                            __stcg(s.ax + slot, ax); __stcg(s.ay + slot, ay); __stcg(s.az + slot, az);
+                            __stcg(s.ts + slot, t);
+                            __stcg(s.id + slot, child_id(id, (unsigned long long)g));
+                        }
+                    }
+                }
+                if (!__any_sync(kFull, alive)) break;
+            }
+            if (in) {
+                if (touched) {
+                    __stcg(s.x + i, x); __stcg(s.y + i, y); __stcg(s.z + i, z);
+                    __stcg(s.vx + i, vx); __stcg(s.vy + i, vy); __stcg(s.vz + i, vz);
+                }
+                // survivors of the last mobility step are "alive since the start" again
+                // (remove_dead_particles writes -1, src/pic.cu:356)
+                const int ts1 = (ts != kDead && t_to == pt) ? -1 : ts;
+                if (ts1 != ts0) __stcg(s.ts + i, ts1);
+            }
+        }
+        if (!kPersistent) break;
+        const int next_hi = mover_barrier_next_window(st, gen++, cap);
+        lo = hi;
+        hi = next_hi;
+        if (lo >= hi) break;
+    }
+    // counters: one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) {
+        my_pushes += __shfl_down_sync(kFull, my_pushes, o);
+        my_dead += __shfl_down_sync(kFull, my_dead, o);
+    }
+    if (lane == 0) {
+        if (my_pushes) atomicAdd(&st->pushes, my_pushes);
+        if (my_dead) atomicAdd(&st->n_dead, my_dead);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Compaction: remove_dead_particles (src/pic.cu:320-357) done IN PLACE.  With S slots and D
+// dead, the survivors must end up in [0, L), L = S - D.  Dead slots below L are "holes",
+// live slots at or above L are "movers"; there are equally many of each.  Pass 1 lists both
+// (warp-aggregated appends), pass 2 copies mover k into hole k.  Traffic is proportional to
+// the number of dead electrons, not to n, and no second capacity-sized buffer exists.
+// ------------------------------------------------------------------------------------------
+__global__ void k_compact_scan(Soa s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
+    const int S = min(st->n_alloc, capacity);
+    const int D = st->n_dead;
+    if (D == 0) return;
+    const int L = S - D;
+    const int lane = threadIdx.x & 31;
+    const int rounded = (S + 31) & ~31;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
+        const bool in = i < S;
+        const bool dead = in && __ldcg(s.ts + i) == kDead;
+        const bool is_hole = dead && i < L;
+        const bool is_mover = in && !dead && i >= L;
+        const unsigned mh = __ballot_sync(kFull, is_hole);
+        const unsigned mm = __ballot_sync(kFull, is_mover);
+        int bh = 0, bm = 0;
+        if (lane == 0) {
+            if (mh) bh = atomicAdd(&st->n_holes, __popc(mh));
+            if (mm) bm = atomicAdd(&st->n_movers, __popc(mm));
+        }
+        bh = __shfl_sync(kFull, bh, 0);
+        bm = __shfl_sync(kFull, bm, 0);
+        if (is_hole) holes[bh + __popc(mh & lanemask_lt())] = i;
+        if (is_mover) movers[bm + __popc(mm & lanemask_lt())] = i;
+    }
+}
+__global__ void k_compact_move(Soa s, const DevState* st, const int* __restrict__ holes, const int* __restrict__ movers) {
+    const int H = min(st->n_holes, st->n_movers);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < H; k += gridDim.x * blockDim.x) {
+        const int src = movers[k], dst = holes[k];
+        s.x[dst] = s.x[src]; s.y[dst] = s.y[src]; s.z[dst] = s.z[src];
+        s.vx[dst] = s.vx[src]; s.vy[dst] = s.vy[src]; s.vz[dst] = s.vz[src];
+        s.ax[dst] = s.ax[src]; s.ay[dst] = s.ay[src]; s.az[dst] = s.az[src];
+        s.ts[dst] = s.ts[src];
+        s.id[dst] = s.id[src];
+    }
+}
+
+// Bookkeeping the reference does on the host after each phase (src/pic.cu:539-559), on the device.
+__global__ void k_mobility_begin(DevState* st) {
+    st->n_alloc = st->n;
+    st->n_dead = 0;
+    st->n_holes = 0; st->n_movers = 0;
+    st->bar_count = 0; st->bar_release = 0;
+}
+__global__ void k_step_end(DevState* st, int capacity, StepLog* log, int log_len, int stop_at_zero) {
+    if (st->hit_zero) return;                      // the reference leaves its loop at "Hit 0"
+    const int n0 = st->n;
+    const int after = st->n_alloc;                 // may overshoot capacity, like the reference's n
+    const int S = min(after, capacity);
+    const int L = S - st->n_dead;
+    st->total_added += (long long)(after - n0);    // src/pic.cu:540
+    st->total_removed += (long long)(after - L);   // src/pic.cu:552
+    st->last_n_after_mobility = after;
+    if (after >= capacity) st->overflow_steps += 1;          // src/pic.cu:544
+    const int p = st->poisson_index;
+    if (log && p < log_len) { log[p].n_after_mobility = after; log[p].n_after_compaction = L; }
+    st->n = L;
+    st->n_alloc = L;
+    st->n_dead = 0; st->n_holes = 0; st->n_movers = 0;
+    // src/pic.cu:556-559; with several ranks an empty slab keeps stepping (the collective needs it)
+    if (L == 0 && stop_at_zero) st->hit_zero = 1;
+    st->poisson_index = p + 1;
+}
+
+// device-side known-answer hooks
+__global__ void k_test_philox(long long n, const uint32_t* ctr, uint2 key, uint32_t* out) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        uint4 r = philox4x32_10(make_uint4(ctr[4 * i], ctr[4 * i + 1], ctr[4 * i + 2], ctr[4 * i + 3]), key);
+        out[4 * i] = r.x; out[4 * i + 1] = r.y; out[4 * i + 2] = r.z; out[4 * i + 3] = r.w;
+    }
+}
+__global__ void k_test_energy_index(long long n, const float* e, const float* tables, int* out) {
+    const float* edge = reinterpret_cast<const float*>(reinterpret_cast<const unsigned char*>(tables) + kThrBytes);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = energy_index(e[i], edge);
+}
+
+}  // namespace picb200

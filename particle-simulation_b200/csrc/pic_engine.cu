@@ -1,0 +1,747 @@
+// pic_engine.cu -- host side of libpicb200.so: the Poisson-loop driver that replaces runPIC
+// (src/pic.cu:359-599 of MagnusMouritzen/particle-simulation) and the C ABI of include/picb200.h.
+//
+// Host C++ only orchestrates: it allocates the SoA electron store and the charge grid once,
+// stages the collision tables, and enqueues kernels that size themselves from a device-resident
+// control block (DevState).  In modes 30/33 a whole run is enqueued without a single host read;
+// modes 31/32 keep the host round trips that define them in the reference.
+#include "pic_device.cuh"
+#include "pic_nccl.h"
+#include "../../include/picb200.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <limits>
+#include <string>
+#include <vector>
+
+namespace picb200 {
+
+static thread_local std::string g_last_error;
+
+static int fail(const std::string& what, const std::string& where) {
+    g_last_error = "CUDA error: " + what + "\nAt: " + where + "\n";   // src/utility.cu:111
+    return 1;
+}
+#define CK(call, where)                                                                  \
+    do {                                                                                 \
+        cudaError_t _e = (call);                                                         \
+        if (_e != cudaSuccess) return fail(cudaGetErrorString(_e), where);               \
+    } while (0)
+#define CK_LAST(where) CK(cudaGetLastError(), where)
+
+// ---- cross-section loader: src/cross_section.cu:3-28 (two floats per row, stop at a short read)
+static int load_table_file(const char* path, std::vector<float>& rows2) {
+    rows2.assign((size_t)kRows * 2, 0.f);
+    std::ifstream in(path);
+    if (!in) return -1;
+    int i = 0;
+    for (; i < kRows; ++i) {
+        float a, b;
+        if (!(in >> a >> b)) break;
+        rows2[2 * (size_t)i] = a;
+        rows2[2 * (size_t)i + 1] = b;
+    }
+    return i;
+}
+
+// The reference's energyToIndex before clamping (src/cross_section.cu:33), on an fp32 energy.
+static inline double ref_index_value(float e) { return std::trunc((std::log10((double)e) + 6) * kRows / 22); }
+
+// edge[j] (1 <= j < kRows) = smallest fp32 energy whose reference index is >= j;
+// edge[0] = 0, edge[kRows] = +inf.  energy_index() on the device probes exactly one entry.
+static void build_energy_edges(float* edge) {
+    edge[0] = 0.f;
+    for (int j = 1; j < kRows; ++j) {
+        float e = (float)std::pow(10.0, -6.0 + 22.0 * (double)j / (double)kRows);
+        while (ref_index_value(e) >= (double)j) e = std::nextafterf(e, 0.f);
+        while (ref_index_value(e) < (double)j) e = std::nextafterf(e, std::numeric_limits<float>::infinity());
+        edge[j] = e;
+    }
+    edge[kRows] = std::numeric_limits<float>::infinity();
+}
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Sim {
+    picb200_config cfg{};
+    int device = 0;
+    int sm_count = 0;
+    int mover_threads = 1024;
+    int blocks_per_sm = 1;
+    int aux_blocks = 0;
+    uint2 seed{};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    Soa soa{};
+    void* soa_base = nullptr;
+    int* charge = nullptr;
+    int* holes = nullptr;
+    int* movers = nullptr;
+    size_t list_cap = 0;
+    float* tables = nullptr;
+    DevState* st = nullptr;
+    DevState* h_st = nullptr;        // pinned mirror
+    StepLog* log = nullptr;
+    int log_len = 0;
+    double efc = 0;
+    double gpu_ms = 0;
+    // multi-GPU
+    NcclApi* nccl = nullptr;
+    void* comm = nullptr;
+    int* box_buf = nullptr;
+    size_t box_buf_cells = 0;
+    int* d_bbox_red = nullptr;
+    int* h_bbox_red = nullptr;
+    // profiling: CUDA-event spans per phase on the launching stream + a count of kernel launches
+    enum Phase { kPhDeposit = 0, kPhGather, kPhClear, kPhMover, kPhCompact, kPhCollective, kPhCount };
+    struct Span { cudaEvent_t a, b; int phase; };
+    int profiling = 0;             // 0 off, 1 scheduler kernels only, 2 every phase
+    std::vector<Span> spans;
+    size_t spans_used = 0;
+    bool span_open = false;
+    double phase_ms[kPhCount] = {0, 0, 0, 0, 0, 0};
+    long long launches = 0, mover_launches = 0;
+    void span_begin(int phase);
+    void span_end();
+    int collect_spans();
+    // optional callback after every launch of the naive scheduler (verbose state dumps, src/pic.cu:528)
+    void (*naive_hook)(Sim*, void*) = nullptr;
+    void* naive_hook_user = nullptr;
+
+    ~Sim() { release(); }
+    void release();
+    int create(const picb200_config* c);
+    int sync_state();
+    int reset_state();
+    int init_uniform(int init_n, unsigned long long id_base);
+    int op_deposit();
+    int op_gather();
+    int op_clear();
+    int op_mobility_begin();
+    int op_mobility();
+    int op_compact();
+    int op_step_end();
+    int poisson_step(bool sync);
+    int launch_mover_window(int lo, int hi, int t_from, int t_to);
+    int allreduce_charge();
+};
+
+void Sim::span_begin(int phase) {
+    span_open = profiling >= 2 || (profiling == 1 && phase == kPhMover);
+    if (!span_open) return;
+    if (spans_used == spans.size()) {
+        Span sp{nullptr, nullptr, 0};
+        cudaEventCreate(&sp.a);
+        cudaEventCreate(&sp.b);
+        spans.push_back(sp);
+    }
+    spans[spans_used].phase = phase;
+    cudaEventRecord(spans[spans_used].a, stream);
+}
+void Sim::span_end() {
+    if (!span_open) return;
+    span_open = false;
+    cudaEventRecord(spans[spans_used].b, stream);
+    ++spans_used;
+}
+// call after the stream has been synchronised
+int Sim::collect_spans() {
+    for (size_t k = 0; k < spans_used; ++k) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, spans[k].a, spans[k].b), "Profile");
+        phase_ms[spans[k].phase] += ms;
+    }
+    spans_used = 0;
+    return 0;
+}
+
+void Sim::release() {
+    for (auto& sp : spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    spans.clear();
+    if (device >= 0 && (soa_base || st)) cudaSetDevice(device);
+    if (comm && nccl) { nccl->commDestroy(comm); comm = nullptr; }
+    if (stream) { cudaStreamSynchronize(stream); }
+    cudaFree(soa_base); soa_base = nullptr;
+    cudaFree(charge); charge = nullptr;
+    cudaFree(holes); holes = nullptr;
+    cudaFree(movers); movers = nullptr;
+    cudaFree(tables); tables = nullptr;
+    cudaFree(st); st = nullptr;
+    cudaFree(log); log = nullptr;
+    cudaFree(box_buf); box_buf = nullptr;
+    cudaFree(d_bbox_red); d_bbox_red = nullptr;
+    if (h_st) { cudaFreeHost(h_st); h_st = nullptr; }
+    if (h_bbox_red) { cudaFreeHost(h_bbox_red); h_bbox_red = nullptr; }
+    if (ev_start) { cudaEventDestroy(ev_start); ev_start = nullptr; }
+    if (ev_stop) { cudaEventDestroy(ev_stop); ev_stop = nullptr; }
+    if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
+}
+
+int Sim::create(const picb200_config* c) {
+    cfg = *c;
+    if (cfg.abi_version != PICB200_ABI_VERSION) return fail("ABI version mismatch", "picb200_create");
+    if (cfg.capacity <= 0 || cfg.poisson_timestep < 0 || cfg.mode < 0 || cfg.mode > 3 || cfg.nranks < 1 ||
+        cfg.rank < 0 || cfg.rank >= cfg.nranks)
+        return fail("invalid configuration", "picb200_create");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail("no CUDA device: libpicb200 has no CPU fallback", "picb200_create");
+    if (cfg.device >= 0) { device = cfg.device; } else { CK(cudaGetDevice(&device), "Get device"); }
+    CK(cudaSetDevice(device), "Set device");
+    CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device), "Device attributes");
+    const unsigned long long sd = cfg.seed ? cfg.seed : 39587ull;      // src/random.cu:4
+    seed = make_uint2((unsigned)sd, (unsigned)(sd >> 32));
+    // logical blocks of `block size` threads share one CTA (and one copy of the shared-memory tables)
+    int bs = std::max(32, std::min(1024, (cfg.block_size / 32) * 32));
+    blocks_per_sm = std::max(1, 1024 / bs);
+    mover_threads = bs * blocks_per_sm;
+    aux_blocks = sm_count * 8;
+    efc = (-1.602176487e-19 * -1.602176487e-19) / (4 * 3.1415926536 * 8.8541878176E-12 * 1e-2 * 1e-2 * 9.1093837015e-31);  // src/cell.cu:5
+
+    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "Stream");
+    CK(cudaEventCreate(&ev_start), "Event");
+    CK(cudaEventCreate(&ev_stop), "Event");
+
+    // ---- collision tables (src/pic.cu:380-386)
+    std::vector<float> rows2;
+    if (cfg.table_rows) {
+        rows2.assign(cfg.table_rows, cfg.table_rows + (size_t)kRows * 2);
+    } else {
+        const char* path = cfg.table_path ? cfg.table_path : "./src/cross_section.txt";
+        int r = load_table_file(path, rows2);
+        if (r < 0) return fail(std::string("Failed to open file: ") + path, "CS Alloc");   // hard error (the reference only warns)
+        if (r < kRows) fprintf(stderr, "Failed to read data for step %d\n", r);           // src/cross_section.cu:17
+    }
+    std::vector<unsigned char> img((size_t)kTableSmemBytes, 0);
+    float* thr = reinterpret_cast<float*>(img.data());
+    for (int i = 0; i < kRows; ++i) {
+        thr[2 * i] = rows2[2 * (size_t)i];                                   // split_chance
+        thr[2 * i + 1] = rows2[2 * (size_t)i + 1] + rows2[2 * (size_t)i];    // remove_chance + split_chance, fp32 (src/particle_move.cu:76)
+    }
+    build_energy_edges(reinterpret_cast<float*>(img.data() + kThrBytes));
+    CK(cudaMalloc(&tables, (size_t)kTableSmemBytes), "CS Alloc");
+    CK(cudaMemcpyAsync(tables, img.data(), (size_t)kTableSmemBytes, cudaMemcpyHostToDevice, stream), "CS Alloc");
+    CK(cudaStreamSynchronize(stream), "CS Alloc");
+
+    // ---- electron store: one allocation, 11 arrays (src/pic.cu:420-424 allocates 2 x cap x 64 B AoS)
+    const size_t cap = (size_t)cfg.capacity;
+    const size_t f_bytes = align_up(cap * 4, 256), id_bytes = align_up(cap * 8, 256);
+    CK(cudaMalloc(&soa_base, f_bytes * 10 + id_bytes), "Electron alloc");
+    unsigned char* p = static_cast<unsigned char*>(soa_base);
+    float** fields[9] = {&soa.x, &soa.y, &soa.z, &soa.vx, &soa.vy, &soa.vz, &soa.ax, &soa.ay, &soa.az};
+    for (auto f : fields) { *f = reinterpret_cast<float*>(p); p += f_bytes; }
+    soa.ts = reinterpret_cast<int*>(p); p += f_bytes;
+    soa.id = reinterpret_cast<unsigned long long*>(p);
+    CK(cudaMemsetAsync(soa.ts, 0, f_bytes, stream), "Electron alloc");
+
+    // ---- compaction work lists: at most min(D, S-D) <= cap/2 entries each
+    list_cap = cap / 2 + 1;
+    CK(cudaMalloc(&holes, list_cap * 4), "Minor alloc");
+    CK(cudaMalloc(&movers, list_cap * 4), "Minor alloc");
+
+    // ---- charge grid 512^3 int32, zeroed once (src/pic.cu:448-450 allocates 2 GiB of 16-B cells)
+    CK(cudaMalloc(&charge, (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
+    CK(cudaMemsetAsync(charge, 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
+
+    CK(cudaMalloc(&st, sizeof(DevState)), "Minor alloc");
+    CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Minor alloc");
+    k_reset_bbox<<<1, 32, 0, stream>>>(st);
+    CK(cudaMallocHost(&h_st, sizeof(DevState)), "Minor alloc");
+    memset(h_st, 0, sizeof(DevState));
+    log_len = std::max(1, cfg.poisson_steps);
+    CK(cudaMalloc(&log, sizeof(StepLog) * (size_t)log_len), "Minor alloc");
+    CK(cudaMemsetAsync(log, 0, sizeof(StepLog) * (size_t)log_len, stream), "Minor alloc");
+
+    CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTableSmemBytes), "Mover attr");
+    CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTableSmemBytes), "Mover attr");
+
+    if (cfg.nranks > 1) {
+        nccl = load_nccl(g_last_error);
+        if (!nccl) return 1;
+        if (!cfg.nccl_unique_id) return fail("nranks > 1 needs nccl_unique_id", "NCCL init");
+        NcclUniqueId id;
+        memcpy(&id, cfg.nccl_unique_id, sizeof(id));
+        int r = nccl->commInitRank(&comm, cfg.nranks, id, cfg.rank);
+        if (r != 0) return fail(std::string("ncclCommInitRank: ") + nccl->getErrorString(r), "NCCL init");
+        CK(cudaMalloc(&d_bbox_red, 8 * sizeof(int)), "Minor alloc");
+        CK(cudaMallocHost(&h_bbox_red, 8 * sizeof(int)), "Minor alloc");
+    }
+    CK(cudaStreamSynchronize(stream), "Setup");
+    CK_LAST("Setup");
+    return 0;
+}
+
+int Sim::sync_state() {
+    CK(cudaMemcpyAsync(h_st, st, sizeof(DevState), cudaMemcpyDeviceToHost, stream), "State readback");
+    CK(cudaStreamSynchronize(stream), "State readback");
+    return collect_spans();
+}
+
+// A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
+int Sim::reset_state() {
+    CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
+    k_reset_bbox<<<1, 32, 0, stream>>>(st);
+    CK_LAST("Reset state");
+    gpu_ms = 0;
+    return 0;
+}
+
+int Sim::init_uniform(int init_n, unsigned long long id_base) {
+    if (init_n < 0 || init_n > cfg.capacity) return fail("init n exceeds capacity", "Setup particles");
+    CK(cudaSetDevice(device), "Set device");
+    if (reset_state()) return 1;
+    k_init_uniform<<<std::max(1, std::min(aux_blocks, (init_n + 255) / 256)), 256, 0, stream>>>(soa, st, init_n, id_base, seed);
+    CK_LAST("Setup particles");
+    return 0;
+}
+
+// ---- grid phase (src/pic.cu:501-504) ---------------------------------------------------------
+int Sim::op_deposit() {
+    span_begin(kPhDeposit);
+    k_deposit<<<aux_blocks, 256, 0, stream>>>(soa, st, charge);
+    ++launches;
+    span_end();
+    CK_LAST("Deposit");
+    if (cfg.nranks > 1) {
+        span_begin(kPhCollective);
+        const int rc = allreduce_charge();
+        span_end();
+        return rc;
+    }
+    return 0;
+}
+int Sim::op_gather() {
+    span_begin(kPhGather);
+    k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, charge, efc);
+    ++launches;
+    span_end();
+    CK_LAST("Gather");
+    return 0;
+}
+int Sim::op_clear() {
+    span_begin(kPhClear);
+    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, charge);
+    k_reset_bbox<<<1, 32, 0, stream>>>(st);
+    launches += 2;
+    span_end();
+    CK_LAST("Clear grid");
+    return 0;
+}
+
+// Sum the charge boxes of all ranks: agree on the union bounding box (max-reduce of
+// {-lo, hi}), pack it contiguously, one integer ncclAllReduce over NVLink, unpack.
+// Integer sums are order-independent, so every rank holds bit-identical counts.
+int Sim::allreduce_charge() {
+    k_bbox_encode<<<1, 32, 0, stream>>>(st, d_bbox_red);
+    launches += 4;   // encode, decode, pack, unpack (NCCL's own kernels are not counted)
+    int r = nccl->allReduce(d_bbox_red, d_bbox_red, 8, kNcclInt32, kNcclMax, comm, stream);
+    if (r != 0) return fail(std::string("ncclAllReduce: ") + nccl->getErrorString(r), "Charge all-reduce");
+    k_bbox_decode<<<1, 32, 0, stream>>>(st, d_bbox_red);
+    CK(cudaMemcpyAsync(h_bbox_red, d_bbox_red, 8 * sizeof(int), cudaMemcpyDeviceToHost, stream), "Charge all-reduce");
+    CK(cudaStreamSynchronize(stream), "Charge all-reduce");
+    const int lx = -h_bbox_red[0], ly = -h_bbox_red[1], lz = -h_bbox_red[2];
+    const int wx = h_bbox_red[3] - lx + 1, wy = h_bbox_red[4] - ly + 1, wz = h_bbox_red[5] - lz + 1;
+    if (wx <= 0 || wy <= 0 || wz <= 0) return 0;
+    const size_t cells = (size_t)wx * wy * wz;
+    if (cells > box_buf_cells) {
+        cudaFree(box_buf);
+        box_buf = nullptr;
+        box_buf_cells = cells + cells / 4;
+        CK(cudaMalloc(&box_buf, box_buf_cells * 4), "Charge all-reduce");
+    }
+    k_pack_box<<<aux_blocks, 256, 0, stream>>>(charge, box_buf, lx, ly, lz, wx, wy, wz, 0);
+    r = nccl->allReduce(box_buf, box_buf, cells, kNcclInt32, kNcclSum, comm, stream);
+    if (r != 0) return fail(std::string("ncclAllReduce: ") + nccl->getErrorString(r), "Charge all-reduce");
+    k_pack_box<<<aux_blocks, 256, 0, stream>>>(charge, box_buf, lx, ly, lz, wx, wy, wz, 1);
+    CK_LAST("Charge all-reduce");
+    return 0;
+}
+
+// ---- mobility phase (src/pic.cu:509-537) -----------------------------------------------------
+int Sim::op_mobility_begin() {
+    k_mobility_begin<<<1, 1, 0, stream>>>(st);
+    ++launches;
+    CK_LAST("Mobility steps");
+    return 0;
+}
+
+int Sim::launch_mover_window(int lo, int hi, int t_from, int t_to) {
+    if (hi <= lo) return 0;
+    MoverArgs a{soa, st, tables, cfg.capacity, cfg.poisson_timestep, lo, hi, t_from, t_to, seed};
+    const int blocks = std::max(1, std::min(sm_count, (hi - lo + mover_threads - 1) / mover_threads));
+    span_begin(kPhMover);
+    k_mover<false><<<blocks, mover_threads, kTableSmemBytes, stream>>>(a);
+    ++launches; ++mover_launches;
+    span_end();
+    CK_LAST("Mobility steps");
+    return 0;
+}
+
+int Sim::op_mobility() {
+    const int pt = cfg.poisson_timestep;
+    switch (cfg.mode) {
+        case PICB200_MODE_DYNAMIC:
+        case PICB200_MODE_DYNAMIC_OLD: {   // one cooperative launch; generations advance on the device
+            MoverArgs a{soa, st, tables, cfg.capacity, pt, 0, 0, 1, pt, seed};
+            void* args[] = {&a};
+            span_begin(kPhMover);
+            CK(cudaLaunchCooperativeKernel((const void*)k_mover<true>, dim3((unsigned)sm_count), dim3((unsigned)mover_threads),
+                                           args, (size_t)kTableSmemBytes, stream),
+               "Mobility steps");
+            ++launches; ++mover_launches;
+            span_end();
+            break;
+        }
+        case PICB200_MODE_CPU_SYNC: {      // src/pic.cu:514-523: relaunch over the new index range until n stops growing
+            if (sync_state()) return 1;
+            int last_n = 0, n_host = std::min(h_st->n_alloc, cfg.capacity);
+            while (n_host != last_n) {
+                if (launch_mover_window(last_n, n_host, 1, pt)) return 1;
+                last_n = n_host;
+                if (sync_state()) return 1;
+                n_host = std::min(h_st->n_alloc, cfg.capacity);
+            }
+            break;
+        }
+        case PICB200_MODE_NAIVE: {         // src/pic.cu:524-532: one launch and one read of n per mobility step
+            if (sync_state()) return 1;
+            for (int t = 1; t <= pt; ++t) {
+                const int n_host = std::min(h_st->n_alloc, cfg.capacity);
+                if (launch_mover_window(0, n_host, t, t)) return 1;
+                if (sync_state()) return 1;
+                if (naive_hook) naive_hook(this, naive_hook_user);
+            }
+            break;
+        }
+    }
+    return 0;
+}
+
+int Sim::op_compact() {
+    span_begin(kPhCompact);
+    k_compact_scan<<<aux_blocks, 256, 0, stream>>>(soa, st, cfg.capacity, holes, movers);
+    k_compact_move<<<aux_blocks, 256, 0, stream>>>(soa, st, holes, movers);
+    launches += 2;
+    span_end();
+    CK_LAST("Remove dead");
+    return 0;
+}
+int Sim::op_step_end() {
+    k_step_end<<<1, 1, 0, stream>>>(st, cfg.capacity, log, log_len, cfg.nranks == 1 ? 1 : 0);
+    ++launches;
+    CK_LAST("Remove dead");
+    return 0;
+}
+
+// One iteration of runPIC's loop (src/pic.cu:487-560).
+int Sim::poisson_step(bool sync) {
+    CK(cudaSetDevice(device), "Set device");
+    if (op_deposit()) return 1;
+    if (op_gather()) return 1;
+    if (op_clear()) return 1;
+    if (op_mobility_begin()) return 1;
+    if (op_mobility()) return 1;
+    if (op_compact()) return 1;
+    if (op_step_end()) return 1;
+    if (sync) return sync_state();
+    return 0;
+}
+
+}  // namespace picb200
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+using namespace picb200;
+struct picb200_sim { Sim s; };
+
+extern "C" {
+
+int picb200_abi_version(void) { return PICB200_ABI_VERSION; }
+const char* picb200_last_error(void) { return g_last_error.c_str(); }
+int picb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+void picb200_config_default(picb200_config* c) {
+    memset(c, 0, sizeof(*c));
+    c->abi_version = PICB200_ABI_VERSION;
+    c->mode = PICB200_MODE_DYNAMIC;
+    c->block_size = 256;
+    c->capacity = 1000000;
+    c->poisson_timestep = 10;
+    c->poisson_steps = 1;
+    c->sleep_time_ns = 100;
+    c->device = -1;
+    c->nranks = 1;
+}
+
+int picb200_create(const picb200_config* cfg, picb200_sim** out) {
+    if (!cfg || !out) return fail("null argument", "picb200_create");
+    picb200_sim* h = new picb200_sim();
+    if (h->s.create(cfg)) { delete h; *out = nullptr; return 1; }
+    *out = h;
+    return 0;
+}
+void picb200_destroy(picb200_sim* sim) { delete sim; }
+
+int picb200_init_uniform(picb200_sim* sim, int32_t init_n, uint64_t id_base) {
+    if (sim->s.init_uniform(init_n, id_base)) return 1;
+    return sim->s.sync_state();
+}
+
+int picb200_upload(picb200_sim* sim, int32_t n, const float* x, const float* y, const float* z, const float* vx,
+                   const float* vy, const float* vz, const float* ax, const float* ay, const float* az,
+                   const int32_t* ts, const uint64_t* id) {
+    Sim& s = sim->s;
+    if (n < 0 || n > s.cfg.capacity || !x || !y || !z) return fail("bad upload arguments", "Upload");
+    CK(cudaSetDevice(s.device), "Set device");
+    const float* src[9] = {x, y, z, vx, vy, vz, ax, ay, az};
+    float* dst[9] = {s.soa.x, s.soa.y, s.soa.z, s.soa.vx, s.soa.vy, s.soa.vz, s.soa.ax, s.soa.ay, s.soa.az};
+    for (int k = 0; k < 9; ++k) {
+        if (src[k]) CK(cudaMemcpyAsync(dst[k], src[k], (size_t)n * 4, cudaMemcpyHostToDevice, s.stream), "Upload");
+        else CK(cudaMemsetAsync(dst[k], 0, (size_t)n * 4, s.stream), "Upload");
+    }
+    std::vector<int32_t> ts_def;
+    std::vector<uint64_t> id_def;
+    if (!ts) { ts_def.assign((size_t)n, -1); ts = ts_def.data(); }
+    if (!id) { id_def.resize((size_t)n); for (int i = 0; i < n; ++i) id_def[(size_t)i] = (uint64_t)i; id = id_def.data(); }
+    CK(cudaMemcpyAsync(s.soa.ts, ts, (size_t)n * 4, cudaMemcpyHostToDevice, s.stream), "Upload");
+    CK(cudaMemcpyAsync(s.soa.id, id, (size_t)n * 8, cudaMemcpyHostToDevice, s.stream), "Upload");
+    if (s.reset_state()) return 1;
+    k_set_n<<<1, 1, 0, s.stream>>>(s.st, n);
+    CK_LAST("Upload");
+    return s.sync_state();
+}
+
+int picb200_download(picb200_sim* sim, int32_t* n_out, float* x, float* y, float* z, float* vx, float* vy, float* vz,
+                     float* ax, float* ay, float* az, int32_t* ts, uint64_t* id) {
+    Sim& s = sim->s;
+    CK(cudaSetDevice(s.device), "Set device");
+    if (s.sync_state()) return 1;
+    const int n = std::min(std::max(s.h_st->n, s.h_st->n_alloc), s.cfg.capacity);
+    float* dst[9] = {x, y, z, vx, vy, vz, ax, ay, az};
+    float* src[9] = {s.soa.x, s.soa.y, s.soa.z, s.soa.vx, s.soa.vy, s.soa.vz, s.soa.ax, s.soa.ay, s.soa.az};
+    for (int k = 0; k < 9; ++k)
+        if (dst[k]) CK(cudaMemcpyAsync(dst[k], src[k], (size_t)n * 4, cudaMemcpyDeviceToHost, s.stream), "Download");
+    if (ts) CK(cudaMemcpyAsync(ts, s.soa.ts, (size_t)n * 4, cudaMemcpyDeviceToHost, s.stream), "Download");
+    if (id) CK(cudaMemcpyAsync(id, s.soa.id, (size_t)n * 8, cudaMemcpyDeviceToHost, s.stream), "Download");
+    CK(cudaStreamSynchronize(s.stream), "Download");
+    if (n_out) *n_out = n;
+    return 0;
+}
+
+int picb200_download_aos(picb200_sim* sim, picb200_electron* out, int64_t cap, int64_t* n_out) {
+    Sim& s = sim->s;
+    if (s.sync_state()) return 1;
+    const int n_all = std::min(std::max(s.h_st->n, s.h_st->n_alloc), s.cfg.capacity);
+    const int n = (int)std::min<int64_t>(n_all, cap);
+    std::vector<float> f((size_t)n * 9);
+    std::vector<int32_t> ts((size_t)n);
+    int got = 0;
+    float* b = f.data();
+    const size_t N = (size_t)n;
+    // download() copies min(n, capacity) entries; restrict by temporarily using sized buffers
+    if (n_all > n) {
+        std::vector<float> g((size_t)n_all * 9);
+        std::vector<int32_t> t2((size_t)n_all);
+        float* q = g.data();
+        const size_t M = (size_t)n_all;
+        if (picb200_download(sim, &got, q, q + M, q + 2 * M, q + 3 * M, q + 4 * M, q + 5 * M, q + 6 * M, q + 7 * M, q + 8 * M, t2.data(), nullptr)) return 1;
+        for (int k = 0; k < 9; ++k) memcpy(b + (size_t)k * N, q + (size_t)k * M, N * 4);
+        memcpy(ts.data(), t2.data(), N * 4);
+    } else if (n > 0) {
+        if (picb200_download(sim, &got, b, b + N, b + 2 * N, b + 3 * N, b + 4 * N, b + 5 * N, b + 6 * N, b + 7 * N, b + 8 * N, ts.data(), nullptr)) return 1;
+    }
+    for (size_t i = 0; i < N; ++i) {
+        picb200_electron& e = out[i];
+        e.position[0] = b[i]; e.position[1] = b[N + i]; e.position[2] = b[2 * N + i];
+        e.velocity[0] = b[3 * N + i]; e.velocity[1] = b[4 * N + i]; e.velocity[2] = b[5 * N + i];
+        e.acceleration[0] = b[6 * N + i]; e.acceleration[1] = b[7 * N + i]; e.acceleration[2] = b[8 * N + i];
+        e.timestamp = ts[i];
+    }
+    if (n_out) *n_out = n;
+    return 0;
+}
+
+int picb200_poisson_step(picb200_sim* sim) { return sim->s.poisson_step(true); }
+
+int picb200_run_steps(picb200_sim* sim, int32_t steps) {
+    Sim& s = sim->s;
+    CK(cudaSetDevice(s.device), "Set device");
+    CK(cudaEventRecord(s.ev_start, s.stream), "Setup");
+    const bool host_in_loop = s.cfg.mode == PICB200_MODE_CPU_SYNC || s.cfg.mode == PICB200_MODE_NAIVE || s.cfg.nranks > 1;
+    for (int t = 0; t < steps; ++t) {
+        if (s.poisson_step(false)) return 1;
+        if (host_in_loop && s.h_st->hit_zero) break;
+    }
+    CK(cudaEventRecord(s.ev_stop, s.stream), "After sim");
+    if (s.sync_state()) return 1;
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, s.ev_start, s.ev_stop), "After sim");
+    s.gpu_ms += ms;
+    return 0;
+}
+
+int picb200_get_summary(picb200_sim* sim, picb200_summary* out) {
+    Sim& s = sim->s;
+    if (s.sync_state()) return 1;
+    memset(out, 0, sizeof(*out));
+    out->final_n = std::min(s.h_st->n, s.cfg.capacity);
+    out->total_added = s.h_st->total_added;
+    out->total_removed = s.h_st->total_removed;
+    out->pushes = (int64_t)s.h_st->pushes;
+    out->poisson_steps_done = s.h_st->poisson_index;
+    out->gpu_ms = s.gpu_ms;
+    out->overflowed = s.h_st->overflow_steps;
+    out->hit_zero = s.h_st->hit_zero;
+    out->sm_count = s.sm_count;
+    out->blocks_per_sm = s.blocks_per_sm;
+    return 0;
+}
+
+int picb200_set_profiling(picb200_sim* sim, int32_t on) {
+    Sim& s = sim->s;
+    if (s.sync_state()) return 1;
+    s.profiling = on;
+    for (double& v : s.phase_ms) v = 0;
+    s.launches = 0; s.mover_launches = 0; s.gpu_ms = 0;
+    return 0;
+}
+int picb200_get_profile(picb200_sim* sim, picb200_profile* out) {
+    Sim& s = sim->s;
+    if (s.sync_state()) return 1;
+    out->deposit_ms = s.phase_ms[Sim::kPhDeposit];
+    out->gather_ms = s.phase_ms[Sim::kPhGather];
+    out->clear_ms = s.phase_ms[Sim::kPhClear];
+    out->mover_ms = s.phase_ms[Sim::kPhMover];
+    out->compact_ms = s.phase_ms[Sim::kPhCompact];
+    out->collective_ms = s.phase_ms[Sim::kPhCollective];
+    out->launches = s.launches;
+    out->mover_launches = s.mover_launches;
+    return 0;
+}
+// Rewrites the whole 512 MiB charge grid with zeros (its value between Poisson steps anyway):
+// 4x the 126 MB L2, so nothing of the electron store stays cached for the next timed run.
+int picb200_flush_l2(picb200_sim* sim) {
+    Sim& s = sim->s;
+    CK(cudaSetDevice(s.device), "Set device");
+    CK(cudaMemsetAsync(s.charge, 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
+    CK(cudaStreamSynchronize(s.stream), "Flush L2");
+    return 0;
+}
+void* picb200_alloc_pinned(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); fail("pinned allocation failed", "picb200_alloc_pinned"); return nullptr; }
+    return p;
+}
+void picb200_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+int picb200_set_poisson_index(picb200_sim* sim, int32_t index) {
+    Sim& s = sim->s;
+    if (s.sync_state()) return 1;
+    s.h_st->poisson_index = index;
+    CK(cudaMemcpyAsync(s.st, s.h_st, sizeof(DevState), cudaMemcpyHostToDevice, s.stream), "Set index");
+    CK(cudaStreamSynchronize(s.stream), "Set index");
+    return 0;
+}
+
+int picb200_op_deposit(picb200_sim* sim) { Sim& s = sim->s; cudaSetDevice(s.device); if (s.op_deposit()) return 1; return s.sync_state(); }
+int picb200_op_gather(picb200_sim* sim) { Sim& s = sim->s; cudaSetDevice(s.device); if (s.op_gather()) return 1; return s.sync_state(); }
+int picb200_op_clear_grid(picb200_sim* sim) { Sim& s = sim->s; cudaSetDevice(s.device); if (s.op_clear()) return 1; return s.sync_state(); }
+int picb200_op_mobility(picb200_sim* sim) {
+    Sim& s = sim->s;
+    cudaSetDevice(s.device);
+    if (s.op_mobility_begin() || s.op_mobility()) return 1;
+    return s.sync_state();
+}
+int picb200_op_compact(picb200_sim* sim) {
+    Sim& s = sim->s;
+    cudaSetDevice(s.device);
+    if (s.op_compact() || s.op_step_end()) return 1;
+    return s.sync_state();
+}
+
+int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3], int32_t* out) {
+    Sim& s = sim->s;
+    cudaSetDevice(s.device);
+    const int wx = hi[0] - lo[0] + 1, wy = hi[1] - lo[1] + 1, wz = hi[2] - lo[2] + 1;
+    if (wx <= 0 || wy <= 0 || wz <= 0 || lo[0] < 0 || lo[1] < 0 || lo[2] < 0 || hi[0] >= kGrid || hi[1] >= kGrid || hi[2] >= kGrid)
+        return fail("bad box", "Charge box");
+    int* buf = nullptr;
+    const size_t cells = (size_t)wx * wy * wz;
+    CK(cudaMalloc(&buf, cells * 4), "Charge box");
+    k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.charge, buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
+    cudaError_t e = cudaMemcpyAsync(out, buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+    cudaFree(buf);
+    CK(e, "Charge box");
+    return 0;
+}
+int picb200_charge_bbox(picb200_sim* sim, int32_t lo[3], int32_t hi[3]) {
+    Sim& s = sim->s;
+    if (s.sync_state()) return 1;
+    for (int k = 0; k < 3; ++k) { lo[k] = s.h_st->bbox_lo[k]; hi[k] = s.h_st->bbox_hi[k]; }
+    return 0;
+}
+
+int picb200_dev_philox(int32_t device, int64_t n, const uint32_t* ctr, const uint32_t* key, uint32_t* out) {
+    if (picb200_device_count() == 0) return fail("no CUDA device", "Philox test");
+    if (device >= 0) CK(cudaSetDevice(device), "Set device");
+    uint32_t *d_c = nullptr, *d_o = nullptr;
+    CK(cudaMalloc(&d_c, (size_t)n * 16), "Philox test");
+    CK(cudaMalloc(&d_o, (size_t)n * 16), "Philox test");
+    CK(cudaMemcpy(d_c, ctr, (size_t)n * 16, cudaMemcpyHostToDevice), "Philox test");
+    k_test_philox<<<64, 256>>>(n, d_c, make_uint2(key[0], key[1]), d_o);
+    cudaError_t e = cudaMemcpy(out, d_o, (size_t)n * 16, cudaMemcpyDeviceToHost);
+    cudaFree(d_c); cudaFree(d_o);
+    CK(e, "Philox test");
+    return 0;
+}
+int picb200_dev_energy_index(int32_t device, int64_t n, const float* energy, int32_t* out) {
+    if (picb200_device_count() == 0) return fail("no CUDA device", "Energy index test");
+    if (device >= 0) CK(cudaSetDevice(device), "Set device");
+    std::vector<unsigned char> img((size_t)kTableSmemBytes, 0);
+    build_energy_edges(reinterpret_cast<float*>(img.data() + kThrBytes));
+    float *d_t = nullptr, *d_e = nullptr;
+    int* d_o = nullptr;
+    CK(cudaMalloc(&d_t, (size_t)kTableSmemBytes), "Energy index test");
+    CK(cudaMalloc(&d_e, (size_t)n * 4), "Energy index test");
+    CK(cudaMalloc(&d_o, (size_t)n * 4), "Energy index test");
+    CK(cudaMemcpy(d_t, img.data(), (size_t)kTableSmemBytes, cudaMemcpyHostToDevice), "Energy index test");
+    CK(cudaMemcpy(d_e, energy, (size_t)n * 4, cudaMemcpyHostToDevice), "Energy index test");
+    k_test_energy_index<<<256, 256>>>(n, d_e, d_t, d_o);
+    cudaError_t e = cudaMemcpy(out, d_o, (size_t)n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(d_t); cudaFree(d_e); cudaFree(d_o);
+    CK(e, "Energy index test");
+    return 0;
+}
+int picb200_load_table(const char* path, float* rows2) {
+    std::vector<float> r;
+    int n = load_table_file(path, r);
+    memcpy(rows2, r.data(), sizeof(float) * 2 * (size_t)kRows);
+    return n;
+}
+// host-side copy of the edge table, for the exhaustive CPU check of the device formula
+void picb200_host_energy_edges(float* out_edges) { build_energy_edges(out_edges); }
+
+int picb200_nccl_unique_id(void* out128) {
+    NcclApi* api = load_nccl(g_last_error);
+    if (!api) return 1;
+    NcclUniqueId id;
+    int r = api->getUniqueId(&id);
+    if (r != 0) return fail(std::string("ncclGetUniqueId: ") + api->getErrorString(r), "NCCL init");
+    memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+}  // extern "C"
+
+#include "pic_run.inl"

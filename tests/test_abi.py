@@ -1,0 +1,92 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads, exports every symbol the
+header declares, and fails loudly (no CPU fallback) when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "picb200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(picb200_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_all_exported(engine):
+    names = declared_symbols()
+    assert len(names) >= 25
+    for n in names:
+        assert hasattr(engine.lib, n), f"{n} declared in include/picb200.h but not exported"
+    assert set(names) == set(engine.SIGNATURES), "binding and header drifted apart"
+
+
+def test_abi_version_and_struct_layout(engine):
+    assert engine.lib.picb200_abi_version() == engine.ABI_VERSION
+    cfg = engine.Config()
+    engine.lib.picb200_config_default(C.byref(cfg))
+    assert (cfg.abi_version, cfg.block_size, cfg.poisson_timestep, cfg.nranks, cfg.device) == (1, 256, 10, 1, -1)
+    assert C.sizeof(engine.Config) == 88 and C.sizeof(engine.Summary) == 64
+    assert engine.ELECTRON_DTYPE.itemsize == 64
+    assert engine.ELECTRON_DTYPE.fields["velocity"][1] == 24 and engine.ELECTRON_DTYPE.fields["timestamp"][1] == 60
+
+
+def test_library_has_no_oracle_dependency(engine):
+    out = subprocess.run(["ldd", engine.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out
+    syms = subprocess.run(["nm", "-D", "--defined-only", engine.LIB_PATH], capture_output=True, text=True).stdout
+    assert "orc_" not in syms
+
+
+def test_loader_matches_oracle_loader(engine, oracle):
+    r, rows = engine.load_table()
+    r2, rows2 = oracle.load_table()
+    assert r == r2 == 10000 and np.array_equal(rows, rows2)
+    assert engine.load_table("/nonexistent/cross_section.txt")[0] == -1
+
+
+def test_edge_table_is_the_reference_formula(engine, oracle):
+    """edge[j] is the smallest fp32 energy whose reference index (double formula) is >= j."""
+    e = engine.host_energy_edges()
+    assert e[0] == 0 and np.isinf(e[-1]) and np.all(np.diff(e[:-1]) > 0)
+    for j in list(range(1, 40)) + [500, 2727, 5000, 9998, 9999]:
+        assert oracle.energy_to_index(float(e[j])) == j
+        assert oracle.energy_to_index(float(np.nextafter(e[j], np.float32(0)))) == j - 1
+
+
+def test_device_energy_index_formula_emulated_on_cpu(engine, tmp_path):
+    """The device's estimate-and-probe index equals the reference formula on a strided sweep of
+    all non-negative fp32 values plus +-3 ulp around every bin edge (the exhaustive sweep,
+    stride 1, passes too: 2 147 553 641 values, 0 mismatches)."""
+    exe = tmp_path / "cei"
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    subprocess.run([cxx, "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fopenmp", "-o", str(exe),
+                    os.path.join(ROOT, "tests", "tools", "check_energy_index.cpp")], check=True)
+    r = subprocess.run([str(exe), "257"], input=engine.host_energy_edges().tobytes(), capture_output=True)
+    assert r.returncode == 0, r.stderr.decode()[:2000]
+    assert b"mismatches 0" in r.stdout
+
+
+@pytest.mark.skipif(os.environ.get("PICB200_EXPECT_GPU") == "1", reason="GPU present")
+def test_no_cpu_fallback(engine):
+    if engine.device_count() > 0:
+        pytest.skip("a CUDA device is visible")
+    with pytest.raises(engine.EngineError, match="no CUDA device"):
+        engine.Sim(capacity=100)
+    with pytest.raises(engine.EngineError):
+        engine.run(init_n=10, capacity=100)
+
+
+def test_cli_usage_without_gpu(engine):
+    r = subprocess.run([engine.CLI_PATH], capture_output=True, text=True)
+    assert r.returncode == 64 and "usage" in r.stderr
+    r = subprocess.run([engine.CLI_PATH, "32", "0", "x", "1", "256", "100", "100", "10"], capture_output=True, text=True)
+    assert r.returncode == 64
+    # unknown mode string: runs nothing, still prints the CPU time (src/main.cu:26-46)
+    r = subprocess.run([engine.CLI_PATH, "99", "0", "10", "1", "256", "100", "100", "10"], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("CPU time of program: ")

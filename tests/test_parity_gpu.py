@@ -1,0 +1,285 @@
+"""GPU parity tests: the CUDA engine (through the C ABI) against the CPU oracle on the same
+seeded inputs.  Integer results (counts, ids, timestamps, cell counts, table indices) must be
+bit-exact; fp32 state is compared bit-exactly too (both sides evaluate the same fp32 expressions
+with explicit fused multiply-adds), which is stricter than north_star's 1e-5 relative bound.
+Particle order is an atomic race on the GPU, so states are compared after sorting by particle id
+-- the reference's own test sorts before comparing as well (src/test.cu:57, :75).
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+MODES = [0, 1, 2, 3]            # Dynamic, CPU Sync, Naive, Dynamic Old  (src/main.cu:26-40)
+F32 = ("x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az")
+
+
+def hot_state(n, seed=1, sigma=0.05):
+    rng = np.random.default_rng(seed)
+    pos = rng.uniform(2.3, 2.8, size=(3, n)).astype(np.float32)
+    vel = (rng.normal(size=(3, n)) * sigma).astype(np.float32)
+    return pos, vel
+
+
+def assert_state_equal(dev_state, orc_sorted, tol=None):
+    d = dev_state.sorted_by_id()
+    assert d.n == len(orc_sorted["id"])
+    assert np.array_equal(d.id, orc_sorted["id"])
+    assert np.array_equal(d.ts, orc_sorted["ts"])
+    for k in F32:
+        a, b = getattr(d, k), orc_sorted[k].astype(np.float32)
+        if tol is None:
+            assert np.array_equal(a, b), f"{k}: {np.sum(a != b)} of {a.size} differ, max rel {np.max(np.abs(a - b) / (np.abs(b) + 1e-30))}"
+        else:
+            assert np.allclose(a, b, rtol=tol, atol=0), k
+
+
+# ------------------------------------------------------------------------------------------
+# arithmetic building blocks, evaluated on the device
+# ------------------------------------------------------------------------------------------
+def test_philox_known_answers_on_device(engine, oracle):
+    from test_oracle import PHILOX_KAT
+    for ctr, key, exp in PHILOX_KAT:
+        assert [int(v) for v in engine.dev_philox(ctr, key)[0]] == exp
+    rng = np.random.default_rng(0)
+    ctr = rng.integers(0, 2 ** 32, size=(4096, 4), dtype=np.uint64).astype(np.uint32)
+    key = np.array([39587, 0], dtype=np.uint32)
+    assert np.array_equal(engine.dev_philox(ctr, key), oracle.philox(ctr, key))
+
+
+def test_energy_index_on_device(engine, oracle):
+    rng = np.random.default_rng(1)
+    edges = engine.host_energy_edges()
+    near = np.concatenate([np.nextafter(edges[1:-1], np.float32(0)), edges[1:-1], np.nextafter(edges[1:-1], np.float32(np.inf))])
+    rnd = (10.0 ** rng.uniform(-12, 20, size=200000)).astype(np.float32)
+    bits = rng.integers(0, 0x7F800000, size=200000, dtype=np.int64).astype(np.uint32).view(np.float32)
+    special = np.array([0.0, 1e-45, 1.17e-38, 1e-6, 1.0, 3.4e38, np.inf, np.nan], dtype=np.float32)
+    e = np.concatenate([near, rnd, bits, special]).astype(np.float32)
+    got = engine.dev_energy_index(e)
+    exp = np.array([oracle.energy_to_index(float(v)) for v in e], dtype=np.int32)
+    assert np.array_equal(got, exp)
+
+
+# ------------------------------------------------------------------------------------------
+# kernels, one phase at a time
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [0, 1, 31, 4097, 100000])
+def test_init_uniform_matches_oracle(engine, oracle, n):
+    with engine.Sim(capacity=max(n, 1) + 5) as sim:
+        sim.init_uniform(n, id_base=7)
+        o = oracle.Oracle(capacity=max(n, 1) + 5, poisson_timestep=10)
+        o.init_uniform(n, 7)
+        assert_state_equal(sim.download(), o.download_sorted())
+
+
+def test_deposit_and_gather_match_oracle(engine, oracle):
+    n = 200000
+    rng = np.random.default_rng(2)
+    # a dense blob (many electrons per cell -> exercises the warp pre-reduction) plus electrons on
+    # the domain faces (absent neighbours count as 0, src/grid_operations.cu:41-52)
+    pos = rng.uniform(2.50, 2.56, size=(3, n)).astype(np.float32)
+    pos[:, :64] = 0.0
+    pos[:, 64:128] = np.float32(5.1199994)
+    pos[0, 128:192] = 0.001
+    with engine.Sim(capacity=n) as sim:
+        sim.upload(*pos)
+        sim.op_deposit()
+        lo, hi = sim.charge_bbox()
+        o = oracle.Oracle(capacity=n, poisson_timestep=10)
+        o.upload(*pos)
+        o.op_deposit()
+        assert list(lo) == [0, 0, 0] and list(hi) == [511, 511, 511]
+        for blo, bhi in (([248, 248, 248], [258, 258, 258]), ([0, 0, 0], [3, 3, 3]), ([508, 508, 508], [511, 511, 511])):
+            got, exp = sim.charge_box(blo, bhi), o.charge_box(blo, bhi)
+            assert np.array_equal(got, exp)
+        assert sim.charge_box([248] * 3, [258] * 3).sum() + 192 >= n - 64  # nothing lost
+        sim.op_gather()
+        o.op_gather()
+        assert_state_equal(sim.download(), o.download_sorted())
+        # clearing restores the all-zero invariant
+        sim.op_clear_grid()
+        assert sim.charge_box([248] * 3, [258] * 3).sum() == 0 and sim.charge_box([0] * 3, [3] * 3).sum() == 0
+        lo, hi = sim.charge_bbox()
+        assert np.all(lo > hi)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n,pt", [(1, 10), (33, 1), (5000, 7), (60000, 10)])
+def test_mobility_phase_matches_oracle(engine, oracle, mode, n, pt):
+    """updateParticle + the scheduler of each mode (src/pic.cu:509-537), collisions switched on."""
+    pos, vel = hot_state(n, seed=n)
+    acc = (np.random.default_rng(5).normal(size=(3, n)) * 3e6).astype(np.float32)
+    cap = 4 * n + 64
+    with engine.Sim(capacity=cap, poisson_timestep=pt, mode=mode) as sim:
+        sim.upload(*pos, *vel, *acc)
+        sim.set_poisson_index(3)
+        sim.op_mobility()
+        o = oracle.Oracle(capacity=cap, poisson_timestep=pt)
+        o.upload(*pos, *vel, *acc)
+        o.set_poisson_index(3)
+        o.op_mobility(stepwise=(mode == 2))
+        assert sim.summary()["pushes"] == o.counters()["pushes"]
+        assert_state_equal(sim.download(), o.download_sorted())
+        sim.op_compact()
+        o.op_compact()
+        d = sim.download()
+        assert np.all(d.ts == -1)
+        assert_state_equal(d, o.download_sorted())
+
+
+def test_out_of_bounds_and_nan(engine, oracle):
+    x = np.array([5.1199994, 2.5, 0.0000001, 2.5], dtype=np.float32)
+    vx = np.array([1e9, 0.0, -1e9, np.nan], dtype=np.float32)
+    y = np.full(4, 2.5, np.float32)
+    for mode in MODES:
+        with engine.Sim(capacity=16, poisson_timestep=4, mode=mode) as sim:
+            sim.upload(x, y, y, vx)
+            sim.op_mobility()
+            o = oracle.Oracle(capacity=16, poisson_timestep=4)
+            o.upload(x, y, y, vx)
+            o.op_mobility(stepwise=(mode == 2))
+            d = sim.download().sorted_by_id()
+            s = o.download_sorted()
+            assert list(d.ts) == list(s["ts"]) and d.ts[0] == -2 and d.ts[2] == -2
+            assert sim.summary()["pushes"] == o.counters()["pushes"]
+
+
+# ------------------------------------------------------------------------------------------
+# whole Poisson steps and whole runs
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", MODES)
+def test_poisson_steps_hot_population(engine, oracle, mode):
+    n, pt, P = 20000, 10, 4
+    pos, vel = hot_state(n, seed=11)
+    with engine.Sim(capacity=200000, poisson_timestep=pt, mode=mode, poisson_steps=P) as sim:
+        sim.upload(*pos, *vel)
+        o = oracle.Oracle(capacity=200000, poisson_timestep=pt)
+        o.upload(*pos, *vel)
+        for step in range(P):
+            sim.poisson_step()
+            o.poisson_step(stepwise=(mode == 2))
+            s, c = sim.summary(), o.counters()
+            assert (s["final_n"], s["total_added"], s["total_removed"], s["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"]), step
+        assert c["added"] > 1000 and c["removed"] > 1000
+        assert_state_equal(sim.download(), o.download_sorted())
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_cfg1_reference_smallest_run(engine, oracle, mode):
+    """BASELINE cfg1: init n 1e4, 10 Poisson steps x 10 mobility steps, capacity 1e6.  Collision
+    free (row 0 of the table is `0.0 0.0`), so added = removed = 0 and the state is RNG-independent."""
+    summ, el = engine.run(electrons=True, mode=mode, init_n=10000, poisson_steps=10, block_size=256, capacity=1000000, poisson_timestep=10)
+    o = oracle.Oracle(capacity=1000000, poisson_timestep=10)
+    o.init_uniform(10000)
+    o.run(10, stepwise=(mode == 2))
+    c = o.counters()
+    assert (summ["final_n"], summ["total_added"], summ["total_removed"], summ["pushes"]) == (10000, 0, 0, 1000000)
+    assert (c["n"], c["added"], c["removed"], c["pushes"]) == (10000, 0, 0, 1000000)
+    s = o.download()          # no spawns, no deaths -> slot order is the id order on both sides
+    assert np.array_equal(el["position"][:, 0].astype(np.float32), s["x"].astype(np.float32))
+    assert np.array_equal(el["velocity"][:, 1].astype(np.float32), s["vy"].astype(np.float32))
+    assert np.array_equal(el["acceleration"][:, 2], s["az"])
+    assert np.all(el["timestamp"] == -1)
+
+
+def test_run_with_collisions_all_modes_agree(engine, oracle):
+    """1e5 electrons for 30 Poisson steps x 10: collisions start after ~100 mobility steps with the
+    shipped table.  All four schedulers and the oracle must produce the same set of electrons."""
+    kw = dict(init_n=100000, poisson_steps=30, capacity=2000000, poisson_timestep=10)
+    o = oracle.Oracle(capacity=2000000, poisson_timestep=10, threads=4)
+    o.init_uniform(100000)
+    o.run(30)
+    c, s = o.counters(), o.download_sorted()
+    assert c["added"] > 100 and c["removed"] > 100
+    for mode in MODES:
+        with engine.Sim(mode=mode, **kw) as sim:
+            sim.init_uniform(100000)
+            sim.run_steps(30)
+            m = sim.summary()
+            assert (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"]), mode
+            assert_state_equal(sim.download(), s)
+
+
+def test_capacity_overflow(engine):
+    rows = np.tile(np.array([[30.0, 0.0]], dtype=np.float32), (10000, 1))
+    pos, vel = hot_state(1000, seed=5)
+    for mode in MODES:
+        with engine.Sim(capacity=1500, poisson_timestep=10, mode=mode, table_rows=rows) as sim:
+            sim.upload(*pos, *vel)
+            sim.poisson_step()
+            m = sim.summary()
+            assert m["final_n"] == 1500 and m["overflowed"] == 1
+            assert m["total_added"] - m["total_removed"] == 500
+            d = sim.download()
+            assert d.n == 1500 and np.all(d.ts == -1) and len(np.unique(d.id)) == 1500
+
+
+def test_population_dies_out(engine):
+    rows = np.tile(np.array([[0.0, 100.0]], dtype=np.float32), (10000, 1))     # every push removes
+    pos, vel = hot_state(500, seed=6)
+    for mode in MODES:
+        with engine.Sim(capacity=1000, poisson_timestep=3, mode=mode, table_rows=rows, poisson_steps=5) as sim:
+            sim.upload(*pos, *vel)
+            sim.run_steps(5)
+            m = sim.summary()
+            assert m["final_n"] == 0 and m["hit_zero"] == 1 and m["total_removed"] == 500 and m["pushes"] == 500
+            assert m["poisson_steps_done"] == 1        # the reference breaks out of its loop (src/pic.cu:556-559)
+
+
+def test_empty_population(engine):
+    summ, _ = engine.run(mode=0, init_n=0, poisson_steps=3, capacity=100, poisson_timestep=10)
+    assert summ["final_n"] == 0 and summ["pushes"] == 0
+
+
+# ------------------------------------------------------------------------------------------
+# size-independent properties at BASELINE's full cfg2 size
+# ------------------------------------------------------------------------------------------
+def test_cfg2_full_size_invariants(engine):
+    """mode 30, init n 1e6, 100 x 10 steps, capacity 1e8 (BASELINE cfg2)."""
+    with engine.Sim(mode=0, init_n=1000000, poisson_steps=100, capacity=100000000, poisson_timestep=10) as sim:
+        sim.init_uniform(1000000)
+        sim.run_steps(100)
+        m = sim.summary()
+        assert m["final_n"] == 1000000 + m["total_added"] - m["total_removed"]
+        assert m["total_added"] > 10000 and m["total_removed"] > 10000 and m["overflowed"] == 0
+        assert 0.9e9 < m["pushes"] < 1.2e9
+        d = sim.download()
+        assert d.n == m["final_n"] and np.all(d.ts == -1)
+        assert len(np.unique(d.id)) == d.n                      # ids stay unique through spawn + compaction
+        for k in "xyz":
+            a = getattr(d, k)
+            assert a.min() > 2.25 and a.max() < 2.89             # nobody left the initial box (dt = 1e-12)
+        sim.op_deposit()
+        lo, hi = sim.charge_bbox()
+        assert sim.charge_box(lo, hi).sum() == d.n               # deposition conserves the count
+
+
+# ------------------------------------------------------------------------------------------
+# the outer boundary: the `run` CLI and its stdout contract
+# ------------------------------------------------------------------------------------------
+def test_cli_stdout_matches_oracle_cli(engine, oracle, tmp_path):
+    """`run 32 1 200 3 256 1000 100 5` prints the reference's lines (src/pic.cu:360, :404, :457-474,
+    :573-576, src/utility.cu:124-137, src/electron.h:19-26).  Collision-free, so the engine's and the
+    oracle's state dumps must be identical text."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    args = ["30", "1", "200", "3", "256", "1000", "100", "5"]
+    a = subprocess.run([os.path.join(root, "run")] + args, capture_output=True, text=True, cwd=root)
+    b = subprocess.run([oracle.CLI] + args, capture_output=True, text=True, cwd=root)
+    assert a.returncode == 0, a.stdout + a.stderr
+
+    def stable(txt):
+        keep = []
+        for ln in txt.splitlines():
+            if ln.startswith(("GPU time of program", "CPU time of program", "Multiprocessor count", "Blocks per multiprocessor")):
+                keep.append(ln.split(":")[0])
+            else:
+                keep.append(ln)
+        return keep
+
+    la, lb = stable(a.stdout), stable(b.stdout)
+    assert la[:7] == ["PIC with", "init n: 200", "capacity: 1000", "poisson steps: 3", "poisson_timestep: 5", "block size: 256", "sleep time: 100"]
+    assert la == lb
+    assert sum(1 for ln in la if ln.startswith("Time ")) == 4 and "Final amount of particles: 200" in la
