@@ -264,6 +264,7 @@ struct MoverArgs {
     const float* tables;   // global image of the shared-memory tables (kTableSmemBytes)
     int capacity, pt;
     int lo, hi, t_from, t_to;   // kPersistent == false only
+    int stepwise;               // mode 32: nobody revisits a child born at the last step, so it is born with ts = -1
     uint2 seed;
 };
 
@@ -389,7 +390,7 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
                             __stcg(s.x + slot, x); __stcg(s.y + slot, y); __stcg(s.z + slot, z);
                             __stcg(s.vx + slot, cvx); __stcg(s.vy + slot, cvy); __stcg(s.vz + slot, cvz);
                             __stcg(s.ax + slot, ax); __stcg(s.ay + slot, ay); __stcg(s.az + slot, az);
-                            __stcg(s.ts + slot, t);
+                            __stcg(s.ts + slot, (a.stepwise && t == pt) ? -1 : t);
                             __stcg(s.id + slot, child_id(id, (unsigned long long)g));
                         }
                     }

@@ -128,7 +128,7 @@ struct Sim {
     int op_compact();
     int op_step_end();
     int poisson_step(bool sync);
-    int launch_mover_window(int lo, int hi, int t_from, int t_to);
+    int launch_mover_window(int lo, int hi, int t_from, int t_to, bool stepwise);
     int allreduce_charge();
 };
 
@@ -371,9 +371,9 @@ int Sim::op_mobility_begin() {
     return 0;
 }
 
-int Sim::launch_mover_window(int lo, int hi, int t_from, int t_to) {
+int Sim::launch_mover_window(int lo, int hi, int t_from, int t_to, bool stepwise) {
     if (hi <= lo) return 0;
-    MoverArgs a{soa, st, tables, cfg.capacity, cfg.poisson_timestep, lo, hi, t_from, t_to, seed};
+    MoverArgs a{soa, st, tables, cfg.capacity, cfg.poisson_timestep, lo, hi, t_from, t_to, stepwise ? 1 : 0, seed};
     const int blocks = std::max(1, std::min(sm_count, (hi - lo + mover_threads - 1) / mover_threads));
     span_begin(kPhMover);
     k_mover<false><<<blocks, mover_threads, kTableSmemBytes, stream>>>(a);
@@ -388,7 +388,7 @@ int Sim::op_mobility() {
     switch (cfg.mode) {
         case PICB200_MODE_DYNAMIC:
         case PICB200_MODE_DYNAMIC_OLD: {   // one cooperative launch; generations advance on the device
-            MoverArgs a{soa, st, tables, cfg.capacity, pt, 0, 0, 1, pt, seed};
+            MoverArgs a{soa, st, tables, cfg.capacity, pt, 0, 0, 1, pt, 0, seed};
             void* args[] = {&a};
             span_begin(kPhMover);
             CK(cudaLaunchCooperativeKernel((const void*)k_mover<true>, dim3((unsigned)sm_count), dim3((unsigned)mover_threads),
@@ -402,7 +402,7 @@ int Sim::op_mobility() {
             if (sync_state()) return 1;
             int last_n = 0, n_host = std::min(h_st->n_alloc, cfg.capacity);
             while (n_host != last_n) {
-                if (launch_mover_window(last_n, n_host, 1, pt)) return 1;
+                if (launch_mover_window(last_n, n_host, 1, pt, false)) return 1;
                 last_n = n_host;
                 if (sync_state()) return 1;
                 n_host = std::min(h_st->n_alloc, cfg.capacity);
@@ -413,7 +413,7 @@ int Sim::op_mobility() {
             if (sync_state()) return 1;
             for (int t = 1; t <= pt; ++t) {
                 const int n_host = std::min(h_st->n_alloc, cfg.capacity);
-                if (launch_mover_window(0, n_host, t, t)) return 1;
+                if (launch_mover_window(0, n_host, t, t, true)) return 1;
                 if (sync_state()) return 1;
                 if (naive_hook) naive_hook(this, naive_hook_user);
             }

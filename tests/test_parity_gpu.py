@@ -24,11 +24,18 @@ def hot_state(n, seed=1, sigma=0.05):
     return pos, vel
 
 
-def assert_state_equal(dev_state, orc_sorted, tol=None):
+def assert_state_equal(dev_state, orc_sorted, tol=None, ts_dead_only=False):
     d = dev_state.sorted_by_id()
     assert d.n == len(orc_sorted["id"])
     assert np.array_equal(d.id, orc_sorted["id"])
-    assert np.array_equal(d.ts, orc_sorted["ts"])
+    if ts_dead_only:
+        # Between the mobility phase and compaction the reference keeps a child's birth step in
+        # `timestamp`; the engine already wrote the -1 that remove_dead_particles would write
+        # (src/pic.cu:356).  Only dead/alive is comparable at that point.
+        assert np.array_equal(d.ts == -2, orc_sorted["ts"] == -2)
+        assert np.all((d.ts == -2) | (d.ts == -1))
+    else:
+        assert np.array_equal(d.ts, orc_sorted["ts"])
     for k in F32:
         a, b = getattr(d, k), orc_sorted[k].astype(np.float32)
         if tol is None:
@@ -122,7 +129,7 @@ def test_mobility_phase_matches_oracle(engine, oracle, mode, n, pt):
         o.set_poisson_index(3)
         o.op_mobility(stepwise=(mode == 2))
         assert sim.summary()["pushes"] == o.counters()["pushes"]
-        assert_state_equal(sim.download(), o.download_sorted())
+        assert_state_equal(sim.download(), o.download_sorted(), ts_dead_only=True)
         sim.op_compact()
         o.op_compact()
         d = sim.download()
@@ -143,7 +150,7 @@ def test_out_of_bounds_and_nan(engine, oracle):
             o.op_mobility(stepwise=(mode == 2))
             d = sim.download().sorted_by_id()
             s = o.download_sorted()
-            assert list(d.ts) == list(s["ts"]) and d.ts[0] == -2 and d.ts[2] == -2
+            assert list(d.ts == -2) == list(s["ts"] == -2) and d.ts[0] == -2 and d.ts[2] == -2
             assert sim.summary()["pushes"] == o.counters()["pushes"]
 
 
