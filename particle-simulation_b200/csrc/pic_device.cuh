@@ -290,6 +290,37 @@ __device__ __forceinline__ int mover_barrier_next_window(DevState* st, unsigned 
     return s_hi;
 }
 
+// Children are staged per warp in shared memory (12 words x 32 entries, field-major so both
+// the ranked writes and the flush reads are bank-conflict free) and appended to the global
+// store 32 at a time: one atomicAdd on n_alloc per flush instead of one per spawning warp-step,
+// and fully coalesced 128-byte stores.  (The reference stages 32 electrons per *block* behind a
+// spin lock, src/pic.cu:25-67, :106-141; a warp-private stage needs no lock at all.)
+constexpr int kStageWords = 12;
+constexpr int kStageBytesPerWarp = kStageWords * 32 * 4;
+constexpr int kMoverSmemBytes(int threads) { return kTableSmemBytes + (threads / 32) * kStageBytesPerWarp; }
+
+__device__ __forceinline__ void stage_flush(const Soa& s, DevState* st, const uint32_t* stage, int count, int cap, int lane) {
+    __syncwarp();
+    int base = 0;
+    if (lane == 0) base = (ld_volatile_i32(&st->n_alloc) < cap) ? atomicAdd(&st->n_alloc, count) : cap;   // `if (*n < capacity)`, src/pic.cu:222
+    base = __shfl_sync(kFull, base, 0);
+    const int slot = base + lane;
+    if (lane < count && slot < cap) {
+        __stcg(s.x + slot, __uint_as_float(stage[0 * 32 + lane]));
+        __stcg(s.y + slot, __uint_as_float(stage[1 * 32 + lane]));
+        __stcg(s.z + slot, __uint_as_float(stage[2 * 32 + lane]));
+        __stcg(s.vx + slot, __uint_as_float(stage[3 * 32 + lane]));
+        __stcg(s.vy + slot, __uint_as_float(stage[4 * 32 + lane]));
+        __stcg(s.vz + slot, __uint_as_float(stage[5 * 32 + lane]));
+        __stcg(s.ax + slot, __uint_as_float(stage[6 * 32 + lane]));
+        __stcg(s.ay + slot, __uint_as_float(stage[7 * 32 + lane]));
+        __stcg(s.az + slot, __uint_as_float(stage[8 * 32 + lane]));
+        __stcg(s.ts + slot, (int)stage[9 * 32 + lane]);
+        __stcg(s.id + slot, ((unsigned long long)stage[11 * 32 + lane] << 32) | stage[10 * 32 + lane]);
+    }
+    __syncwarp();
+}
+
 template <bool kPersistent>
 __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -305,6 +336,8 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     DevState* st = a.st;
     const Soa s = a.s;
     const int cap = a.capacity, pt = a.pt;
+    uint32_t* stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * 32);
+    int staged = 0;                       // warp-uniform: children waiting in this warp's stage
     const unsigned g0 = (unsigned)st->poisson_index * (unsigned)pt;
     const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
     const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
@@ -375,25 +408,21 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
                         }
                     }
                 }
-                // warp-aggregated append into [n_alloc, capacity)  (cf. src/pic.cu:219-229, :276-287)
+                // spawn: rank the children of this warp-step into the warp's stage (cf. src/pic.cu:106-141)
                 const unsigned m = __ballot_sync(kFull, spawn);
                 if (m) {
-                    const int leader = __ffs(m) - 1;
-                    int base = 0;
-                    if (lane == leader) {
-                        base = (ld_volatile_i32(&st->n_alloc) < cap) ? atomicAdd(&st->n_alloc, __popc(m)) : cap;
-                    }
-                    base = __shfl_sync(kFull, base, leader);
+                    const int cnt = __popc(m);
+                    if (staged + cnt > 32) { stage_flush(s, st, stage, staged, cap, lane); staged = 0; }
                     if (spawn) {
-                        const int slot = base + __popc(m & lanemask_lt());
-                        if (slot < cap) {
-                            __stcg(s.x + slot, x); __stcg(s.y + slot, y); __stcg(s.z + slot, z);
-                            __stcg(s.vx + slot, cvx); __stcg(s.vy + slot, cvy); __stcg(s.vz + slot, cvz);
-                            __stcg(s.ax + slot, ax); __stcg(s.ay + slot, ay); __stcg(s.az + slot, az);
-                            __stcg(s.ts + slot, (a.stepwise && t == pt) ? -1 : t);
-                            __stcg(s.id + slot, child_id(id, (unsigned long long)g));
-                        }
+                        const int r = staged + __popc(m & lanemask_lt());
+                        const unsigned long long cid = child_id(id, (unsigned long long)g);
+                        stage[0 * 32 + r] = __float_as_uint(x); stage[1 * 32 + r] = __float_as_uint(y); stage[2 * 32 + r] = __float_as_uint(z);
+                        stage[3 * 32 + r] = __float_as_uint(cvx); stage[4 * 32 + r] = __float_as_uint(cvy); stage[5 * 32 + r] = __float_as_uint(cvz);
+                        stage[6 * 32 + r] = __float_as_uint(ax); stage[7 * 32 + r] = __float_as_uint(ay); stage[8 * 32 + r] = __float_as_uint(az);
+                        stage[9 * 32 + r] = (uint32_t)((a.stepwise && t == pt) ? -1 : t);
+                        stage[10 * 32 + r] = (uint32_t)cid; stage[11 * 32 + r] = (uint32_t)(cid >> 32);
                     }
+                    staged += cnt;
                 }
                 if (!__any_sync(kFull, alive)) break;
             }
@@ -408,6 +437,7 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
                 if (ts1 != ts0) __stcg(s.ts + i, ts1);
             }
         }
+        if (staged) { stage_flush(s, st, stage, staged, cap, lane); staged = 0; }   // children must be visible before the window advances
         if (!kPersistent) break;
         const int next_hi = mover_barrier_next_window(st, gen++, cap);
         lo = hi;

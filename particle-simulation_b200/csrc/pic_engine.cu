@@ -258,8 +258,8 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&log, sizeof(StepLog) * (size_t)log_len), "Minor alloc");
     CK(cudaMemsetAsync(log, 0, sizeof(StepLog) * (size_t)log_len, stream), "Minor alloc");
 
-    CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTableSmemBytes), "Mover attr");
-    CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTableSmemBytes), "Mover attr");
+    CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
     if (cfg.nranks > 1) {
         nccl = load_nccl(g_last_error);
@@ -376,7 +376,7 @@ int Sim::launch_mover_window(int lo, int hi, int t_from, int t_to, bool stepwise
     MoverArgs a{soa, st, tables, cfg.capacity, cfg.poisson_timestep, lo, hi, t_from, t_to, stepwise ? 1 : 0, seed};
     const int blocks = std::max(1, std::min(sm_count, (hi - lo + mover_threads - 1) / mover_threads));
     span_begin(kPhMover);
-    k_mover<false><<<blocks, mover_threads, kTableSmemBytes, stream>>>(a);
+    k_mover<false><<<blocks, mover_threads, kMoverSmemBytes(mover_threads), stream>>>(a);
     ++launches; ++mover_launches;
     span_end();
     CK_LAST("Mobility steps");
@@ -392,7 +392,7 @@ int Sim::op_mobility() {
             void* args[] = {&a};
             span_begin(kPhMover);
             CK(cudaLaunchCooperativeKernel((const void*)k_mover<true>, dim3((unsigned)sm_count), dim3((unsigned)mover_threads),
-                                           args, (size_t)kTableSmemBytes, stream),
+                                           args, (size_t)kMoverSmemBytes(mover_threads), stream),
                "Mobility steps");
             ++launches; ++mover_launches;
             span_end();
