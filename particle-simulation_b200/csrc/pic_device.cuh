@@ -42,6 +42,8 @@ struct DevState {
     int n_holes, n_movers;  // compaction work lists
     unsigned bar_count, bar_release;   // grid barrier of the persistent mover
     int gen_hi;             // generation window end agreed at the barrier
+    int ticket;             // next unclaimed 32-electron chunk of the generation-0 window
+    int n_unfinished;       // children spilled to the global store before they were pushed to the end
     int bbox_lo[3], bbox_hi[3];        // cell bounding box of the charge currently deposited
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)
@@ -248,212 +250,7 @@ __global__ void k_pack_box(const int* __restrict__ charge, int* __restrict__ buf
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// K_mover: leapfrog + bounds + Monte-Carlo collision (updateParticle, src/particle_move.cu:22-87)
-// under the three scheduling disciplines of src/pic.cu:
-//   kPersistent = true : modes 30/33 -- one cooperative launch per Poisson step; electrons stay
-//       in registers for all remaining mobility steps; children are appended with one
-//       warp-aggregated atomic and consumed generation by generation inside the same launch
-//       (a device-side queue window [lo,hi) advanced at a grid barrier) -- no host round trip.
-//   kPersistent = false: mode 31 (host passes the window of one generation) and mode 32
-//       (host passes t_from == t_to, one mobility step per launch).
-// ------------------------------------------------------------------------------------------
-struct MoverArgs {
-    Soa s;
-    DevState* st;
-    const float* tables;   // global image of the shared-memory tables (kTableSmemBytes)
-    int capacity, pt;
-    int lo, hi, t_from, t_to;   // kPersistent == false only
-    int stepwise;               // mode 32: nobody revisits a child born at the last step, so it is born with ts = -1
-    uint2 seed;
-};
-
-__device__ __forceinline__ int mover_barrier_next_window(DevState* st, unsigned gen, int capacity) {
-    __shared__ int s_hi;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        const unsigned target = (gen + 1u) * gridDim.x;
-        const unsigned prev = atomicAdd(&st->bar_count, 1u);
-        if (prev + 1u == target) {           // last block to arrive fixes the next window
-            __threadfence();
-            st->gen_hi = min(ld_volatile_i32(&st->n_alloc), capacity);
-            __threadfence();
-            atomicExch(&st->bar_release, gen + 1u);
-        } else {
-            while (ld_acquire_u32(&st->bar_release) < gen + 1u) __nanosleep(64);
-        }
-        __threadfence();
-        s_hi = ld_volatile_i32(&st->gen_hi);
-    }
-    __syncthreads();
-    return s_hi;
-}
-
-// Children are staged per warp in shared memory (12 words x 32 entries, field-major so both
-// the ranked writes and the flush reads are bank-conflict free) and appended to the global
-// store 32 at a time: one atomicAdd on n_alloc per flush instead of one per spawning warp-step,
-// and fully coalesced 128-byte stores.  (The reference stages 32 electrons per *block* behind a
-// spin lock, src/pic.cu:25-67, :106-141; a warp-private stage needs no lock at all.)
-constexpr int kStageWords = 12;
-constexpr int kStageBytesPerWarp = kStageWords * 32 * 4;
-constexpr int kMoverSmemBytes(int threads) { return kTableSmemBytes + (threads / 32) * kStageBytesPerWarp; }
-
-__device__ __forceinline__ void stage_flush(const Soa& s, DevState* st, const uint32_t* stage, int count, int cap, int lane) {
-    __syncwarp();
-    int base = 0;
-    if (lane == 0) base = (ld_volatile_i32(&st->n_alloc) < cap) ? atomicAdd(&st->n_alloc, count) : cap;   // `if (*n < capacity)`, src/pic.cu:222
-    base = __shfl_sync(kFull, base, 0);
-    const int slot = base + lane;
-    if (lane < count && slot < cap) {
-        __stcg(s.x + slot, __uint_as_float(stage[0 * 32 + lane]));
-        __stcg(s.y + slot, __uint_as_float(stage[1 * 32 + lane]));
-        __stcg(s.z + slot, __uint_as_float(stage[2 * 32 + lane]));
-        __stcg(s.vx + slot, __uint_as_float(stage[3 * 32 + lane]));
-        __stcg(s.vy + slot, __uint_as_float(stage[4 * 32 + lane]));
-        __stcg(s.vz + slot, __uint_as_float(stage[5 * 32 + lane]));
-        __stcg(s.ax + slot, __uint_as_float(stage[6 * 32 + lane]));
-        __stcg(s.ay + slot, __uint_as_float(stage[7 * 32 + lane]));
-        __stcg(s.az + slot, __uint_as_float(stage[8 * 32 + lane]));
-        __stcg(s.ts + slot, (int)stage[9 * 32 + lane]);
-        __stcg(s.id + slot, ((unsigned long long)stage[11 * 32 + lane] << 32) | stage[10 * 32 + lane]);
-    }
-    __syncwarp();
-}
-
-template <bool kPersistent>
-__global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const float2* s_thr = reinterpret_cast<const float2*>(smem_raw);
-    const float* s_edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
-    {   // stage the collision tables (120 KB) once per CTA, 128-bit copies
-        const float4* src = reinterpret_cast<const float4*>(a.tables);
-        float4* dst = reinterpret_cast<float4*>(smem_raw);
-        for (int k = threadIdx.x; k < kTableSmemBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
-    }
-    __syncthreads();
-
-    DevState* st = a.st;
-    const Soa s = a.s;
-    const int cap = a.capacity, pt = a.pt;
-    uint32_t* stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * 32);
-    int staged = 0;                       // warp-uniform: children waiting in this warp's stage
-    const unsigned g0 = (unsigned)st->poisson_index * (unsigned)pt;
-    const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
-    const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
-    const int lane = threadIdx.x & 31;
-    int lo, hi, t_from, t_to;
-    if (kPersistent) { lo = 0; hi = min(st->n, cap); t_from = 1; t_to = pt; }
-    else { lo = a.lo; hi = a.hi; t_from = a.t_from; t_to = a.t_to; }
-
-    unsigned long long my_pushes = 0;
-    int my_dead = 0;
-    unsigned gen = 0;
-    for (;;) {
-        const int span = hi - lo;
-        const int rounded = (span + 31) & ~31;
-        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += gridDim.x * blockDim.x) {
-            const int i = lo + k;
-            const bool in = k < span;
-            float x = 0, y = 0, z = 0, vx = 0, vy = 0, vz = 0, ax = 0, ay = 0, az = 0;
-            int ts = kDead;
-            unsigned long long id = 0;
-            if (in) {
-                x = __ldcg(s.x + i); y = __ldcg(s.y + i); z = __ldcg(s.z + i);
-                vx = __ldcg(s.vx + i); vy = __ldcg(s.vy + i); vz = __ldcg(s.vz + i);
-                ax = __ldcg(s.ax + i); ay = __ldcg(s.ay + i); az = __ldcg(s.az + i);
-                ts = __ldcg(s.ts + i);
-                id = __ldcg(s.id + i);
-            }
-            const int ts0 = ts;
-            bool alive = in && ts != kDead;
-            // first step of this electron: max(1, timestamp+1)  (src/pic.cu:218)
-            const int t0 = alive ? max(t_from, max(1, ts + 1)) : 0x7fffffff;
-            const int t_begin = __reduce_min_sync(kFull, t0);
-            bool touched = false;
-            uint4 rnd = make_uint4(0, 0, 0, 0);
-            unsigned cur_blk = 0xffffffffu;
-            for (int t = t_begin; t <= t_to; ++t) {
-                bool spawn = false;
-                float cvx = 0, cvy = 0, cvz = 0;
-                const unsigned g = g0 + (unsigned)t;
-                if (alive && t >= t0) {
-                    touched = true;
-                    ++my_pushes;
-                    // leapfrog, src/particle_move.cu:22-39
-                    vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
-                    x = __fmaf_rn(vx, dt, x); y = __fmaf_rn(vy, dt, y); z = __fmaf_rn(vz, dt, z);
-                    vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
-                    // checkOutOfBounds, src/particle_move.cu:41-52 (no draw consumed)
-                    if (x < 0.f || x >= sim || y < 0.f || y >= sim || z < 0.f || z >= sim) {
-                        alive = false; ts = kDead; ++my_dead;
-                    } else {
-                        // collider, src/particle_move.cu:55-80
-                        const unsigned blk = g >> 2;
-                        if (blk != cur_blk) {
-                            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), blk, kTagCollide), a.seed);
-                            cur_blk = blk;
-                        }
-                        const unsigned sel = g & 3u;
-                        const uint32_t w = sel == 0 ? rnd.x : (sel == 1 ? rnd.y : (sel == 2 ? rnd.z : rnd.w));
-                        const float r = __fmul_rn(uniform01(w), 100.0f);
-                        const float e = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
-                        const float2 th = s_thr[energy_index(e, s_edge)];
-                        if (r < th.x) {              // ionisation: child copies the pre-flip state
-                            spawn = true;
-                            cvx = vx; cvy = vy; cvz = vz;
-                            vx = -vx; vy = -vy; vz = -vz;
-                        } else if (r < th.y) {       // attachment: electron removed
-                            alive = false; ts = kDead; ++my_dead;
-                        }
-                    }
-                }
-                // spawn: rank the children of this warp-step into the warp's stage (cf. src/pic.cu:106-141)
-                const unsigned m = __ballot_sync(kFull, spawn);
-                if (m) {
-                    const int cnt = __popc(m);
-                    if (staged + cnt > 32) { stage_flush(s, st, stage, staged, cap, lane); staged = 0; }
-                    if (spawn) {
-                        const int r = staged + __popc(m & lanemask_lt());
-                        const unsigned long long cid = child_id(id, (unsigned long long)g);
-                        stage[0 * 32 + r] = __float_as_uint(x); stage[1 * 32 + r] = __float_as_uint(y); stage[2 * 32 + r] = __float_as_uint(z);
-                        stage[3 * 32 + r] = __float_as_uint(cvx); stage[4 * 32 + r] = __float_as_uint(cvy); stage[5 * 32 + r] = __float_as_uint(cvz);
-                        stage[6 * 32 + r] = __float_as_uint(ax); stage[7 * 32 + r] = __float_as_uint(ay); stage[8 * 32 + r] = __float_as_uint(az);
-                        stage[9 * 32 + r] = (uint32_t)((a.stepwise && t == pt) ? -1 : t);
-                        stage[10 * 32 + r] = (uint32_t)cid; stage[11 * 32 + r] = (uint32_t)(cid >> 32);
-                    }
-                    staged += cnt;
-                }
-                if (!__any_sync(kFull, alive)) break;
-            }
-            if (in) {
-                if (touched) {
-                    __stcg(s.x + i, x); __stcg(s.y + i, y); __stcg(s.z + i, z);
-                    __stcg(s.vx + i, vx); __stcg(s.vy + i, vy); __stcg(s.vz + i, vz);
-                }
-                // survivors of the last mobility step are "alive since the start" again
-                // (remove_dead_particles writes -1, src/pic.cu:356)
-                const int ts1 = (ts != kDead && t_to == pt) ? -1 : ts;
-                if (ts1 != ts0) __stcg(s.ts + i, ts1);
-            }
-        }
-        if (staged) { stage_flush(s, st, stage, staged, cap, lane); staged = 0; }   // children must be visible before the window advances
-        if (!kPersistent) break;
-        const int next_hi = mover_barrier_next_window(st, gen++, cap);
-        lo = hi;
-        hi = next_hi;
-        if (lo >= hi) break;
-    }
-    // counters: one atomic per warp
-    for (int o = 16; o > 0; o >>= 1) {
-        my_pushes += __shfl_down_sync(kFull, my_pushes, o);
-        my_dead += __shfl_down_sync(kFull, my_dead, o);
-    }
-    if (lane == 0) {
-        if (my_pushes) atomicAdd(&st->pushes, my_pushes);
-        if (my_dead) atomicAdd(&st->n_dead, my_dead);
-    }
-}
+#include "pic_mover.cuh"
 
 // ------------------------------------------------------------------------------------------
 // Compaction: remove_dead_particles (src/pic.cu:320-357) done IN PLACE.  With S slots and D
@@ -505,6 +302,7 @@ __global__ void k_mobility_begin(DevState* st) {
     st->n_dead = 0;
     st->n_holes = 0; st->n_movers = 0;
     st->bar_count = 0; st->bar_release = 0;
+    st->ticket = 0; st->n_unfinished = 0;
 }
 __global__ void k_step_end(DevState* st, int capacity, StepLog* log, int log_len, int stop_at_zero) {
     if (st->hit_zero) return;                      // the reference leaves its loop at "Hit 0"

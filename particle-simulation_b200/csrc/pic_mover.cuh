@@ -1,0 +1,312 @@
+// pic_mover.cuh -- the scheduler kernels (included inside namespace picb200 by pic_device.cuh).
+//
+// K_mover: leapfrog + bounds + Monte-Carlo collision (updateParticle, src/particle_move.cu:22-87)
+// under the scheduling disciplines of src/pic.cu:
+//   kPersistent = true  (modes 30/33): ONE cooperative launch per Poisson step.  Warps claim
+//       32-electron chunks of the population with a ticket counter; an electron stays in
+//       registers for all its remaining mobility steps.  Children are ranked into a warp-private
+//       stage in shared memory and the SAME warp later pushes them to the end of the Poisson step
+//       straight out of that stage, so a child normally reaches the global store exactly once, in
+//       its final state, and no grid-wide synchronisation separates "generations".  Only if a
+//       stage overflows are unfinished children spilled to the global store; a grid barrier at the
+//       end detects that and a fall-back pass finishes them.  The host never sees any of it
+//       (contrast src/pic.cu:70-211: block-wide spin lock, polling of timestamps, host reset of
+//       four counters per Poisson step).
+//   kPersistent = false: mode 31 (the host passes the index window of one generation of children,
+//       src/pic.cu:514-523) and mode 32 (t_from == t_to: one mobility step per launch,
+//       src/pic.cu:524-532).  Children are always flushed unfinished, as those modes require.
+
+struct MoverArgs {
+    Soa s;
+    DevState* st;
+    const float* tables;   // global image of the shared-memory tables (kTableSmemBytes)
+    int capacity, pt;
+    int lo, hi, t_from, t_to;   // kPersistent == false only
+    int stepwise;               // mode 32: nobody revisits a child born at the last step, so it is born with ts = -1
+    uint2 seed;
+};
+
+// Children are staged per warp in shared memory: 12 words x 32 entries, field-major, so both the
+// ranked writes and the lane-indexed reads are bank-conflict free.
+constexpr int kStageWords = 12;
+constexpr int kStageBytesPerWarp = kStageWords * 32 * 4;
+constexpr int kMoverSmemBytes(int threads) { return kTableSmemBytes + (threads / 32) * kStageBytesPerWarp; }
+constexpr int kDrainThreshold = 16;   // push staged children once this many wait
+
+struct El {
+    float x, y, z, vx, vy, vz, ax, ay, az;
+    unsigned long long id;
+};
+
+struct MoverCtx {
+    Soa s;
+    DevState* st;
+    const float2* thr;
+    const float* edge;
+    uint32_t* stage;
+    int cap, pt, lane, stepwise;
+    unsigned g0;
+    uint2 seed;
+};
+
+// Reserve `count` consecutive slots of the global store: one atomic per call, honouring the
+// reference's `if (*n < capacity)` pre-check (src/pic.cu:222).  Returns the first slot (>= cap: none).
+__device__ __forceinline__ int reserve_slots(const MoverCtx& c, int count) {
+    int base = 0;
+    if (c.lane == 0) base = (ld_volatile_i32(&c.st->n_alloc) < c.cap) ? atomicAdd(&c.st->n_alloc, count) : c.cap;
+    return __shfl_sync(kFull, base, 0);
+}
+
+// Write the staged children to the global store as they are (timestamp = birth step): they still
+// need their remaining pushes.  kCount: tell the persistent kernel's fall-back pass they exist.
+template <bool kCount>
+__device__ __forceinline__ void stage_spill(const MoverCtx& c, int count) {
+    __syncwarp();
+    const int slot = reserve_slots(c, count) + c.lane;
+    const bool w = c.lane < count && slot < c.cap;
+    if (w) {
+        const uint32_t* g = c.stage + c.lane;
+        __stcg(c.s.x + slot, __uint_as_float(g[0 * 32])); __stcg(c.s.y + slot, __uint_as_float(g[1 * 32])); __stcg(c.s.z + slot, __uint_as_float(g[2 * 32]));
+        __stcg(c.s.vx + slot, __uint_as_float(g[3 * 32])); __stcg(c.s.vy + slot, __uint_as_float(g[4 * 32])); __stcg(c.s.vz + slot, __uint_as_float(g[5 * 32]));
+        __stcg(c.s.ax + slot, __uint_as_float(g[6 * 32])); __stcg(c.s.ay + slot, __uint_as_float(g[7 * 32])); __stcg(c.s.az + slot, __uint_as_float(g[8 * 32]));
+        __stcg(c.s.ts + slot, (int)g[9 * 32]);
+        __stcg(c.s.id + slot, ((unsigned long long)g[11 * 32] << 32) | g[10 * 32]);
+    }
+    if (kCount) {
+        const unsigned m = __ballot_sync(kFull, w);
+        if (c.lane == 0 && m) atomicAdd(&c.st->n_unfinished, __popc(m));
+    }
+    __syncwarp();
+}
+
+// Push one lane's electron through mobility steps max(t_begin.., t0) .. t_to; all 32 lanes run the
+// same step together.  Spawned children are ranked into the warp's stage.
+template <bool kCountSpill>
+__device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, int t0, int t_to, int& staged,
+                                        unsigned& pushes, int& dead, bool& touched) {
+    const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
+    const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
+    const int t_begin = __reduce_min_sync(kFull, alive ? t0 : 0x7fffffff);
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+    unsigned cur_blk = 0xffffffffu;
+    for (int t = t_begin; t <= t_to; ++t) {
+        bool spawn = false;
+        float cvx = 0, cvy = 0, cvz = 0;
+        const unsigned g = c.g0 + (unsigned)t;
+        if (alive && t >= t0) {
+            touched = true;
+            ++pushes;
+            // leapfrog, src/particle_move.cu:22-39
+            e.vx = __fmaf_rn(-e.ax, hdt, e.vx); e.vy = __fmaf_rn(-e.ay, hdt, e.vy); e.vz = __fmaf_rn(-e.az, hdt, e.vz);
+            e.x = __fmaf_rn(e.vx, dt, e.x); e.y = __fmaf_rn(e.vy, dt, e.y); e.z = __fmaf_rn(e.vz, dt, e.z);
+            e.vx = __fmaf_rn(-e.ax, hdt, e.vx); e.vy = __fmaf_rn(-e.ay, hdt, e.vy); e.vz = __fmaf_rn(-e.az, hdt, e.vz);
+            // checkOutOfBounds, src/particle_move.cu:41-52 (no draw consumed)
+            // (written as the reference writes it: a NaN coordinate is NOT out of bounds)
+            const bool oob = (e.x < 0.f) | (e.x >= sim) | (e.y < 0.f) | (e.y >= sim) | (e.z < 0.f) | (e.z >= sim);
+            if (oob) {
+                alive = false; ++dead;
+            } else {
+                // collider, src/particle_move.cu:55-80
+                const unsigned blk = g >> 2;
+                if (blk != cur_blk) {
+                    rnd = philox4x32_10(make_uint4((uint32_t)e.id, (uint32_t)(e.id >> 32), blk, kTagCollide), c.seed);
+                    cur_blk = blk;
+                }
+                const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
+                const uint32_t w = (g & 2u) ? w23 : w01;
+                const float r = __fmul_rn(uniform01(w), 100.0f);
+                const float en = __fmaf_rn(e.vz, e.vz, __fmaf_rn(e.vy, e.vy, __fmul_rn(e.vx, e.vx)));
+                const float2 th = c.thr[energy_index(en, c.edge)];
+                if (r < th.x) {              // ionisation: the child copies the pre-flip state
+                    spawn = true;
+                    cvx = e.vx; cvy = e.vy; cvz = e.vz;
+                    e.vx = -e.vx; e.vy = -e.vy; e.vz = -e.vz;
+                } else if (r < th.y) {       // attachment: electron removed
+                    alive = false; ++dead;
+                }
+            }
+        }
+        const unsigned m = __ballot_sync(kFull, spawn);
+        if (m) {
+            const int cnt = __popc(m);
+            if (staged + cnt > 32) { stage_spill<kCountSpill>(c, staged); staged = 0; }
+            if (spawn) {
+                uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
+                const unsigned long long cid = child_id(e.id, (unsigned long long)g);
+                q[0 * 32] = __float_as_uint(e.x); q[1 * 32] = __float_as_uint(e.y); q[2 * 32] = __float_as_uint(e.z);
+                q[3 * 32] = __float_as_uint(cvx); q[4 * 32] = __float_as_uint(cvy); q[5 * 32] = __float_as_uint(cvz);
+                q[6 * 32] = __float_as_uint(e.ax); q[7 * 32] = __float_as_uint(e.ay); q[8 * 32] = __float_as_uint(e.az);
+                q[9 * 32] = (uint32_t)((c.stepwise && t == c.pt) ? -1 : t);
+                q[10 * 32] = (uint32_t)cid; q[11 * 32] = (uint32_t)(cid >> 32);
+            }
+            staged += cnt;
+        }
+        if (!__any_sync(kFull, alive)) break;
+    }
+}
+
+// One 32-electron chunk straight from the global store: slots [i0, i0+32) clipped to `end`.
+// kLaterGen: fall-back pass of the persistent kernel -- only spilled children (ts >= 0) need work.
+template <bool kCountSpill, bool kLaterGen>
+__device__ __forceinline__ void process_chunk(const MoverCtx& c, int i0, int end, int t_from, int t_to, int& staged,
+                                              unsigned& pushes, int& dead) {
+    const int i = i0 + c.lane;
+    const bool in = i < end;
+    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int ts = kDead;
+    if (in) {
+        e.x = __ldcg(c.s.x + i); e.y = __ldcg(c.s.y + i); e.z = __ldcg(c.s.z + i);
+        e.vx = __ldcg(c.s.vx + i); e.vy = __ldcg(c.s.vy + i); e.vz = __ldcg(c.s.vz + i);
+        e.ax = __ldcg(c.s.ax + i); e.ay = __ldcg(c.s.ay + i); e.az = __ldcg(c.s.az + i);
+        ts = __ldcg(c.s.ts + i);
+        e.id = __ldcg(c.s.id + i);
+    }
+    const bool was_alive = in && (kLaterGen ? ts >= 0 : ts != kDead);
+    bool alive = was_alive;
+    // first step of this electron: max(1, timestamp+1)  (src/pic.cu:218)
+    const int t0 = max(t_from, max(1, ts + 1));
+    bool touched = false;
+    advance<kCountSpill>(c, e, alive, t0, t_to, staged, pushes, dead, touched);
+    if (was_alive) {
+        if (touched) {
+            __stcg(c.s.x + i, e.x); __stcg(c.s.y + i, e.y); __stcg(c.s.z + i, e.z);
+            __stcg(c.s.vx + i, e.vx); __stcg(c.s.vy + i, e.vy); __stcg(c.s.vz + i, e.vz);
+        }
+        // survivors of the last mobility step are "alive since the start" again
+        // (remove_dead_particles writes -1, src/pic.cu:356)
+        const int ts1 = !alive ? kDead : (t_to == c.pt ? -1 : ts);
+        if (ts1 != ts) __stcg(c.s.ts + i, ts1);
+    }
+}
+
+// Persistent kernel only: the warp takes the children waiting in its own stage into registers,
+// reserves their final slots, pushes them to the end of the Poisson step (grandchildren go to the
+// now empty stage) and writes each of them to the global store once, finished.
+__device__ __forceinline__ void process_staged(const MoverCtx& c, int& staged, unsigned& pushes, int& dead) {
+    const int k = staged;
+    __syncwarp();
+    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int tb = 0;
+    if (c.lane < k) {
+        const uint32_t* g = c.stage + c.lane;
+        e.x = __uint_as_float(g[0 * 32]); e.y = __uint_as_float(g[1 * 32]); e.z = __uint_as_float(g[2 * 32]);
+        e.vx = __uint_as_float(g[3 * 32]); e.vy = __uint_as_float(g[4 * 32]); e.vz = __uint_as_float(g[5 * 32]);
+        e.ax = __uint_as_float(g[6 * 32]); e.ay = __uint_as_float(g[7 * 32]); e.az = __uint_as_float(g[8 * 32]);
+        tb = (int)g[9 * 32];
+        e.id = ((unsigned long long)g[11 * 32] << 32) | g[10 * 32];
+    }
+    staged = 0;
+    __syncwarp();
+    const int slot = reserve_slots(c, k) + c.lane;
+    const bool in = c.lane < k && slot < c.cap;      // children past the capacity are dropped (src/pic.cu:224)
+    bool alive = in;
+    bool touched = false;
+    advance<true>(c, e, alive, tb + 1, c.pt, staged, pushes, dead, touched);
+    if (in) {
+        __stcg(c.s.x + slot, e.x); __stcg(c.s.y + slot, e.y); __stcg(c.s.z + slot, e.z);
+        __stcg(c.s.vx + slot, e.vx); __stcg(c.s.vy + slot, e.vy); __stcg(c.s.vz + slot, e.vz);
+        __stcg(c.s.ax + slot, e.ax); __stcg(c.s.ay + slot, e.ay); __stcg(c.s.az + slot, e.az);
+        __stcg(c.s.ts + slot, alive ? -1 : kDead);
+        __stcg(c.s.id + slot, e.id);
+    }
+}
+
+// Grid barrier of the persistent kernel.  The last block to arrive decides whether a fall-back
+// pass is needed: it publishes the end of the window that may hold spilled children, or -1.
+__device__ __forceinline__ int mover_barrier_next_window(DevState* st, unsigned gen, int capacity) {
+    __shared__ int s_hi;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned target = (gen + 1u) * gridDim.x;
+        const unsigned prev = atomicAdd(&st->bar_count, 1u);
+        if (prev + 1u == target) {
+            __threadfence();
+            const int unfinished = ld_volatile_i32(&st->n_unfinished);
+            st->n_unfinished = 0;
+            st->gen_hi = unfinished > 0 ? min(ld_volatile_i32(&st->n_alloc), capacity) : -1;
+            __threadfence();
+            atomicExch(&st->bar_release, gen + 1u);
+        } else {
+            while (ld_acquire_u32(&st->bar_release) < gen + 1u) __nanosleep(64);
+        }
+        __threadfence();
+        s_hi = ld_volatile_i32(&st->gen_hi);
+    }
+    __syncthreads();
+    return s_hi;
+}
+
+template <bool kPersistent>
+__global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    {   // stage the collision tables (120 KB) once per CTA, 128-bit copies
+        const float4* src = reinterpret_cast<const float4*>(a.tables);
+        float4* dst = reinterpret_cast<float4*>(smem_raw);
+        for (int k = threadIdx.x; k < kTableSmemBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
+    }
+    __syncthreads();
+
+    MoverCtx c;
+    c.s = a.s;
+    c.st = a.st;
+    c.thr = reinterpret_cast<const float2*>(smem_raw);
+    c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
+    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * 32);
+    c.cap = a.capacity;
+    c.pt = a.pt;
+    c.lane = threadIdx.x & 31;
+    c.stepwise = a.stepwise;
+    c.g0 = (unsigned)a.st->poisson_index * (unsigned)a.pt;
+    c.seed = a.seed;
+
+    int staged = 0;            // warp-uniform: children waiting in this warp's stage
+    unsigned pushes = 0;
+    int dead = 0;
+
+    if (kPersistent) {
+        const int n0 = min(a.st->n, c.cap);
+        const int chunks = (n0 + 31) >> 5;
+        // generation 0: chunks are claimed with a ticket; the next ticket is requested before the
+        // current chunk is processed so its latency hides behind the pushes
+        int next = 0;
+        if (c.lane == 0) next = atomicAdd(&a.st->ticket, 1);
+        for (;;) {
+            const int chunk = __shfl_sync(kFull, next, 0);
+            if (chunk >= chunks) break;
+            if (c.lane == 0) next = atomicAdd(&a.st->ticket, 1);
+            process_chunk<true, false>(c, chunk << 5, n0, 1, c.pt, staged, pushes, dead);
+            if (staged >= kDrainThreshold) process_staged(c, staged, pushes, dead);
+        }
+        while (staged) process_staged(c, staged, pushes, dead);
+        // fall-back passes: only if some stage overflowed and spilled unfinished children
+        int lo = n0;
+        for (unsigned gen = 0;; ++gen) {
+            const int hi = mover_barrier_next_window(a.st, gen, c.cap);
+            if (hi < 0) break;
+            const int rounded = (hi - lo + 31) & ~31;
+            for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x) {
+                process_chunk<true, true>(c, lo + k, hi, 1, c.pt, staged, pushes, dead);
+                if (staged >= kDrainThreshold) process_staged(c, staged, pushes, dead);
+            }
+            while (staged) process_staged(c, staged, pushes, dead);
+            lo = hi;
+        }
+    } else {
+        const int span = a.hi - a.lo;
+        const int rounded = (span + 31) & ~31;
+        for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x)
+            process_chunk<false, false>(c, a.lo + k, a.hi, a.t_from, a.t_to, staged, pushes, dead);
+        if (staged) { stage_spill<false>(c, staged); staged = 0; }
+    }
+
+    // counters: one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) {
+        pushes += __shfl_down_sync(kFull, pushes, o);
+        dead += __shfl_down_sync(kFull, dead, o);
+    }
+    if (c.lane == 0) {
+        if (pushes) atomicAdd(&a.st->pushes, (unsigned long long)pushes);
+        if (dead) atomicAdd(&a.st->n_dead, dead);
+    }
+}
