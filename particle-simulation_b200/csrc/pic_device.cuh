@@ -36,21 +36,26 @@ struct Soa {
 // step (or a whole run) is enqueued without the host ever reading a counter back
 // (contrast src/pic.cu:495-497, :539, :551: three blocking copies per Poisson step).
 struct DevState {
+    // -- line 0: step bookkeeping (cold inside a mobility phase)
     int n;                  // live electrons = slots [0,n); all ts == -1 between Poisson steps
-    int n_alloc;            // append cursor during the mobility phase (may overshoot capacity)
-    int n_dead;             // electrons marked DEAD in this Poisson step
     int n_holes, n_movers;  // compaction work lists
-    unsigned bar_count, bar_release;   // grid barrier of the persistent mover
-    int gen_hi;             // generation window end agreed at the barrier
-    int ticket;             // next unclaimed 32-electron chunk of the generation-0 window
+    int gen_hi;             // end of the fall-back window agreed at the barrier (-1: none)
     int n_unfinished;       // children spilled to the global store before they were pushed to the end
-    int bbox_lo[3], bbox_hi[3];        // cell bounding box of the charge currently deposited
+    int bbox_lo[2][3], bbox_hi[2][3];  // cell bounding box of the counts deposited in charge grid 0 / 1
+    int cur;                // which of the two charge grids holds the current deposit
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)
     int overflow_steps;     // steps whose n reached capacity (src/pic.cu:544)
     int last_n_after_mobility;
-    unsigned long long pushes;         // updateParticle evaluations
+    int ticket;             // (spare work counter)
     long long total_added, total_removed;
+    // -- hot atomics, one 128-byte line each so they do not serialise behind one another in L2
+    alignas(128) int n_alloc;                   // append cursor during the mobility phase (may overshoot capacity)
+    alignas(128) int n_dead;                    // electrons marked DEAD in this Poisson step
+    alignas(128) unsigned long long pushes;     // updateParticle evaluations
+    alignas(128) unsigned bar_count;            // grid barrier: arrivals
+    alignas(128) unsigned bar_release;          // grid barrier: releases
+    alignas(128) int pad_;
 };
 
 struct StepLog { int n_after_mobility, n_after_compaction; };
@@ -155,7 +160,7 @@ __global__ void k_init_uniform(Soa s, DevState* st, int init_n, unsigned long lo
 // warp-level pre-reduction (__match_any_sync groups lanes that hit the same cell; one
 // red.global.add per group) and a block-reduced cell bounding box.
 // ------------------------------------------------------------------------------------------
-__global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge) {
+__global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge, int which) {
     __shared__ int s_lo[3], s_hi[3];
     if (threadIdx.x < 3) { s_lo[threadIdx.x] = kGrid; s_hi[threadIdx.x] = -1; }
     __syncthreads();
@@ -183,8 +188,8 @@ __global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge) {
     }
     __syncthreads();
     if (threadIdx.x < 3 && s_hi[threadIdx.x] >= 0) {
-        atomicMin(&st->bbox_lo[threadIdx.x], s_lo[threadIdx.x]);
-        atomicMax(&st->bbox_hi[threadIdx.x], s_hi[threadIdx.x]);
+        atomicMin(&st->bbox_lo[which][threadIdx.x], s_lo[threadIdx.x]);
+        atomicMax(&st->bbox_hi[which][threadIdx.x], s_hi[threadIdx.x]);
     }
 }
 
@@ -212,30 +217,36 @@ __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ char
 }
 
 // K_clear: resetGrid (src/grid_operations.cu:6-12) restricted to the deposited bounding box.
-__global__ void k_clear_box(const DevState* st, int* __restrict__ charge) {
-    const int lx = st->bbox_lo[0], ly = st->bbox_lo[1], lz = st->bbox_lo[2];
-    const int wx = st->bbox_hi[0] - lx + 1, wy = st->bbox_hi[1] - ly + 1, wz = st->bbox_hi[2] - lz + 1;
+__device__ __forceinline__ void clear_box_body(const DevState* st, int* __restrict__ charge, int which) {
+    const int lx = ld_volatile_i32(&st->bbox_lo[which][0]), ly = ld_volatile_i32(&st->bbox_lo[which][1]), lz = ld_volatile_i32(&st->bbox_lo[which][2]);
+    const int wx = ld_volatile_i32(&st->bbox_hi[which][0]) - lx + 1, wy = ld_volatile_i32(&st->bbox_hi[which][1]) - ly + 1,
+              wz = ld_volatile_i32(&st->bbox_hi[which][2]) - lz + 1;
     if (wx <= 0 || wy <= 0 || wz <= 0) return;
     const long long total = (long long)wx * wy * wz;
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
         const int x = (int)(k % wx);
         const long long r = k / wx;
         const int y = (int)(r % wy), z = (int)(r / wy);
-        charge[cell_index(lx + x, ly + y, lz + z)] = 0;
+        __stcg(charge + cell_index(lx + x, ly + y, lz + z), 0);
     }
 }
+__global__ void k_clear_box(const DevState* st, int* __restrict__ charge, int which) { clear_box_body(st, charge, which); }
 __global__ void k_set_n(DevState* st, int n) { st->n = n; st->n_alloc = n; }
-__global__ void k_reset_bbox(DevState* st) {
-    if (threadIdx.x < 3) { st->bbox_lo[threadIdx.x] = kGrid; st->bbox_hi[threadIdx.x] = -1; }
+// which: 0 / 1 = that grid's box, 2 = both
+__global__ void k_reset_bbox(DevState* st, int which) {
+    if (threadIdx.x < 3) {
+        if (which != 1) { st->bbox_lo[0][threadIdx.x] = kGrid; st->bbox_hi[0][threadIdx.x] = -1; }
+        if (which != 0) { st->bbox_lo[1][threadIdx.x] = kGrid; st->bbox_hi[1][threadIdx.x] = -1; }
+    }
 }
 
 // Multi-GPU: the union bounding box is one max-reduction of {-lo[3], hi[3], 0, 0}.
-__global__ void k_bbox_encode(const DevState* st, int* red) {
-    if (threadIdx.x < 3) { red[threadIdx.x] = -st->bbox_lo[threadIdx.x]; red[3 + threadIdx.x] = st->bbox_hi[threadIdx.x]; }
+__global__ void k_bbox_encode(const DevState* st, int* red, int which) {
+    if (threadIdx.x < 3) { red[threadIdx.x] = -st->bbox_lo[which][threadIdx.x]; red[3 + threadIdx.x] = st->bbox_hi[which][threadIdx.x]; }
     if (threadIdx.x >= 6 && threadIdx.x < 8) red[threadIdx.x] = 0;
 }
-__global__ void k_bbox_decode(DevState* st, const int* red) {
-    if (threadIdx.x < 3) { st->bbox_lo[threadIdx.x] = -red[threadIdx.x]; st->bbox_hi[threadIdx.x] = red[3 + threadIdx.x]; }
+__global__ void k_bbox_decode(DevState* st, const int* red, int which) {
+    if (threadIdx.x < 3) { st->bbox_lo[which][threadIdx.x] = -red[threadIdx.x]; st->bbox_hi[which][threadIdx.x] = red[3 + threadIdx.x]; }
 }
 
 // pack / unpack the charge box into a contiguous buffer for the multi-GPU all-reduce
@@ -250,8 +261,6 @@ __global__ void k_pack_box(const int* __restrict__ charge, int* __restrict__ buf
     }
 }
 
-#include "pic_mover.cuh"
-
 // ------------------------------------------------------------------------------------------
 // Compaction: remove_dead_particles (src/pic.cu:320-357) done IN PLACE.  With S slots and D
 // dead, the survivors must end up in [0, L), L = S - D.  Dead slots below L are "holes",
@@ -259,9 +268,9 @@ __global__ void k_pack_box(const int* __restrict__ charge, int* __restrict__ buf
 // (warp-aggregated appends), pass 2 copies mover k into hole k.  Traffic is proportional to
 // the number of dead electrons, not to n, and no second capacity-sized buffer exists.
 // ------------------------------------------------------------------------------------------
-__global__ void k_compact_scan(Soa s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
-    const int S = min(st->n_alloc, capacity);
-    const int D = st->n_dead;
+__device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
+    const int S = min(ld_volatile_i32(&st->n_alloc), capacity);
+    const int D = ld_volatile_i32(&st->n_dead);
     if (D == 0) return;
     const int L = S - D;
     const int lane = threadIdx.x & 31;
@@ -280,20 +289,26 @@ __global__ void k_compact_scan(Soa s, DevState* st, int capacity, int* __restric
         }
         bh = __shfl_sync(kFull, bh, 0);
         bm = __shfl_sync(kFull, bm, 0);
-        if (is_hole) holes[bh + __popc(mh & lanemask_lt())] = i;
-        if (is_mover) movers[bm + __popc(mm & lanemask_lt())] = i;
+        if (is_hole) __stcg(holes + bh + __popc(mh & lanemask_lt()), i);
+        if (is_mover) __stcg(movers + bm + __popc(mm & lanemask_lt()), i);
+    }
+}
+__global__ void k_compact_scan(Soa s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
+    compact_scan_body(s, st, capacity, holes, movers);
+}
+__device__ __forceinline__ void compact_move_body(const Soa& s, const DevState* st, const int* holes, const int* movers) {
+    const int H = min(ld_volatile_i32(&st->n_holes), ld_volatile_i32(&st->n_movers));
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < H; k += gridDim.x * blockDim.x) {
+        const int src = __ldcg(movers + k), dst = __ldcg(holes + k);
+        __stcg(s.x + dst, __ldcg(s.x + src)); __stcg(s.y + dst, __ldcg(s.y + src)); __stcg(s.z + dst, __ldcg(s.z + src));
+        __stcg(s.vx + dst, __ldcg(s.vx + src)); __stcg(s.vy + dst, __ldcg(s.vy + src)); __stcg(s.vz + dst, __ldcg(s.vz + src));
+        __stcg(s.ax + dst, __ldcg(s.ax + src)); __stcg(s.ay + dst, __ldcg(s.ay + src)); __stcg(s.az + dst, __ldcg(s.az + src));
+        __stcg(s.ts + dst, __ldcg(s.ts + src));
+        __stcg(s.id + dst, __ldcg(s.id + src));
     }
 }
 __global__ void k_compact_move(Soa s, const DevState* st, const int* __restrict__ holes, const int* __restrict__ movers) {
-    const int H = min(st->n_holes, st->n_movers);
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < H; k += gridDim.x * blockDim.x) {
-        const int src = movers[k], dst = holes[k];
-        s.x[dst] = s.x[src]; s.y[dst] = s.y[src]; s.z[dst] = s.z[src];
-        s.vx[dst] = s.vx[src]; s.vy[dst] = s.vy[src]; s.vz[dst] = s.vz[src];
-        s.ax[dst] = s.ax[src]; s.ay[dst] = s.ay[src]; s.az[dst] = s.az[src];
-        s.ts[dst] = s.ts[src];
-        s.id[dst] = s.id[src];
-    }
+    compact_move_body(s, st, holes, movers);
 }
 
 // Bookkeeping the reference does on the host after each phase (src/pic.cu:539-559), on the device.
@@ -304,16 +319,17 @@ __global__ void k_mobility_begin(DevState* st) {
     st->bar_count = 0; st->bar_release = 0;
     st->ticket = 0; st->n_unfinished = 0;
 }
-__global__ void k_step_end(DevState* st, int capacity, StepLog* log, int log_len, int stop_at_zero) {
+__device__ __forceinline__ void step_end_body(DevState* st_, int capacity, StepLog* log, int log_len, int stop_at_zero) {
+    volatile DevState* st = st_;                   // also runs inside the fused kernel: never through a stale L1 line
     if (st->hit_zero) return;                      // the reference leaves its loop at "Hit 0"
     const int n0 = st->n;
     const int after = st->n_alloc;                 // may overshoot capacity, like the reference's n
     const int S = min(after, capacity);
     const int L = S - st->n_dead;
-    st->total_added += (long long)(after - n0);    // src/pic.cu:540
-    st->total_removed += (long long)(after - L);   // src/pic.cu:552
+    st->total_added = st->total_added + (long long)(after - n0);    // src/pic.cu:540
+    st->total_removed = st->total_removed + (long long)(after - L); // src/pic.cu:552
     st->last_n_after_mobility = after;
-    if (after >= capacity) st->overflow_steps += 1;          // src/pic.cu:544
+    if (after >= capacity) st->overflow_steps = st->overflow_steps + 1;   // src/pic.cu:544
     const int p = st->poisson_index;
     if (log && p < log_len) { log[p].n_after_mobility = after; log[p].n_after_compaction = L; }
     st->n = L;
@@ -323,6 +339,11 @@ __global__ void k_step_end(DevState* st, int capacity, StepLog* log, int log_len
     if (L == 0 && stop_at_zero) st->hit_zero = 1;
     st->poisson_index = p + 1;
 }
+__global__ void k_step_end(DevState* st, int capacity, StepLog* log, int log_len, int stop_at_zero) {
+    step_end_body(st, capacity, log, log_len, stop_at_zero);
+}
+
+#include "pic_mover.cuh"
 
 // device-side known-answer hooks
 __global__ void k_test_philox(long long n, const uint32_t* ctr, uint2 key, uint32_t* out) {

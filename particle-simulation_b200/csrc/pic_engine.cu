@@ -66,6 +66,19 @@ static void build_energy_edges(float* edge) {
     edge[kRows] = std::numeric_limits<float>::infinity();
 }
 
+// bnd[k] (1 <= k < kGrid) = smallest fp32 coordinate whose cell index int(double(x)/1e-2)
+// (src/grid_operations.cu:21-23) is >= k; bnd[0] = -inf, bnd[kGrid] = +inf.
+static void build_cell_bounds(float* bnd) {
+    bnd[0] = -std::numeric_limits<float>::infinity();
+    for (int k = 1; k < kGrid; ++k) {
+        float x = (float)((double)k * 1e-2);
+        while ((double)x / 1e-2 >= (double)k) x = std::nextafterf(x, 0.f);
+        while ((double)x / 1e-2 < (double)k) x = std::nextafterf(x, std::numeric_limits<float>::infinity());
+        bnd[k] = x;
+    }
+    bnd[kGrid] = std::numeric_limits<float>::infinity();
+}
+
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct Sim {
@@ -80,7 +93,9 @@ struct Sim {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     Soa soa{};
     void* soa_base = nullptr;
-    int* charge = nullptr;
+    int* grid[2] = {nullptr, nullptr};   // two charge grids: gather from one while the next deposit fills the other
+    int cur = 0;                         // host view of DevState::cur (valid after every sync)
+    bool charge_valid = false;           // grid[cur] holds the deposit of the current population
     int* holes = nullptr;
     int* movers = nullptr;
     size_t list_cap = 0;
@@ -128,6 +143,8 @@ struct Sim {
     int op_compact();
     int op_step_end();
     int poisson_step(bool sync);
+    int fused_steps(int steps);
+    bool fused = false;                  // modes 30/33: whole Poisson steps inside one cooperative kernel
     int launch_mover_window(int lo, int hi, int t_from, int t_to, bool stepwise);
     int allreduce_charge();
 };
@@ -168,7 +185,8 @@ void Sim::release() {
     if (comm && nccl) { nccl->commDestroy(comm); comm = nullptr; }
     if (stream) { cudaStreamSynchronize(stream); }
     cudaFree(soa_base); soa_base = nullptr;
-    cudaFree(charge); charge = nullptr;
+    cudaFree(grid[0]); grid[0] = nullptr;
+    cudaFree(grid[1]); grid[1] = nullptr;
     cudaFree(holes); holes = nullptr;
     cudaFree(movers); movers = nullptr;
     cudaFree(tables); tables = nullptr;
@@ -218,15 +236,16 @@ int Sim::create(const picb200_config* c) {
         if (r < 0) return fail(std::string("Failed to open file: ") + path, "CS Alloc");   // hard error (the reference only warns)
         if (r < kRows) fprintf(stderr, "Failed to read data for step %d\n", r);           // src/cross_section.cu:17
     }
-    std::vector<unsigned char> img((size_t)kTableSmemBytes, 0);
+    std::vector<unsigned char> img((size_t)kAllTableBytes, 0);
     float* thr = reinterpret_cast<float*>(img.data());
+    build_cell_bounds(reinterpret_cast<float*>(img.data() + kTableSmemBytes));
     for (int i = 0; i < kRows; ++i) {
         thr[2 * i] = rows2[2 * (size_t)i];                                   // split_chance
         thr[2 * i + 1] = rows2[2 * (size_t)i + 1] + rows2[2 * (size_t)i];    // remove_chance + split_chance, fp32 (src/particle_move.cu:76)
     }
     build_energy_edges(reinterpret_cast<float*>(img.data() + kThrBytes));
-    CK(cudaMalloc(&tables, (size_t)kTableSmemBytes), "CS Alloc");
-    CK(cudaMemcpyAsync(tables, img.data(), (size_t)kTableSmemBytes, cudaMemcpyHostToDevice, stream), "CS Alloc");
+    CK(cudaMalloc(&tables, (size_t)kAllTableBytes), "CS Alloc");
+    CK(cudaMemcpyAsync(tables, img.data(), (size_t)kAllTableBytes, cudaMemcpyHostToDevice, stream), "CS Alloc");
     CK(cudaStreamSynchronize(stream), "CS Alloc");
 
     // ---- electron store: one allocation, 11 arrays (src/pic.cu:420-424 allocates 2 x cap x 64 B AoS)
@@ -246,12 +265,14 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&movers, list_cap * 4), "Minor alloc");
 
     // ---- charge grid 512^3 int32, zeroed once (src/pic.cu:448-450 allocates 2 GiB of 16-B cells)
-    CK(cudaMalloc(&charge, (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
-    CK(cudaMemsetAsync(charge, 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
+    for (int g = 0; g < 2; ++g) {
+        CK(cudaMalloc(&grid[g], (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
+        CK(cudaMemsetAsync(grid[g], 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
+    }
 
     CK(cudaMalloc(&st, sizeof(DevState)), "Minor alloc");
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Minor alloc");
-    k_reset_bbox<<<1, 32, 0, stream>>>(st);
+    k_reset_bbox<<<1, 32, 0, stream>>>(st, 2);
     CK(cudaMallocHost(&h_st, sizeof(DevState)), "Minor alloc");
     memset(h_st, 0, sizeof(DevState));
     log_len = std::max(1, cfg.poisson_steps);
@@ -259,6 +280,8 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMemsetAsync(log, 0, sizeof(StepLog) * (size_t)log_len, stream), "Minor alloc");
 
     CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
     if (cfg.nranks > 1) {
@@ -280,15 +303,21 @@ int Sim::create(const picb200_config* c) {
 int Sim::sync_state() {
     CK(cudaMemcpyAsync(h_st, st, sizeof(DevState), cudaMemcpyDeviceToHost, stream), "State readback");
     CK(cudaStreamSynchronize(stream), "State readback");
+    cur = h_st->cur;
     return collect_spans();
 }
 
 // A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
 int Sim::reset_state() {
+    // a deposit of the previous population may still sit in either grid: both boxes bound it
+    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[0], 0);
+    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[1], 1);
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
-    k_reset_bbox<<<1, 32, 0, stream>>>(st);
+    k_reset_bbox<<<1, 32, 0, stream>>>(st, 2);
     CK_LAST("Reset state");
     gpu_ms = 0;
+    cur = 0;
+    charge_valid = false;
     return 0;
 }
 
@@ -304,7 +333,8 @@ int Sim::init_uniform(int init_n, unsigned long long id_base) {
 // ---- grid phase (src/pic.cu:501-504) ---------------------------------------------------------
 int Sim::op_deposit() {
     span_begin(kPhDeposit);
-    k_deposit<<<aux_blocks, 256, 0, stream>>>(soa, st, charge);
+    k_deposit<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], cur);
+    charge_valid = true;
     ++launches;
     span_end();
     CK_LAST("Deposit");
@@ -318,7 +348,7 @@ int Sim::op_deposit() {
 }
 int Sim::op_gather() {
     span_begin(kPhGather);
-    k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, charge, efc);
+    k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc);
     ++launches;
     span_end();
     CK_LAST("Gather");
@@ -326,8 +356,9 @@ int Sim::op_gather() {
 }
 int Sim::op_clear() {
     span_begin(kPhClear);
-    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, charge);
-    k_reset_bbox<<<1, 32, 0, stream>>>(st);
+    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[cur], cur);
+    k_reset_bbox<<<1, 32, 0, stream>>>(st, cur);
+    charge_valid = false;
     launches += 2;
     span_end();
     CK_LAST("Clear grid");
@@ -338,11 +369,11 @@ int Sim::op_clear() {
 // {-lo, hi}), pack it contiguously, one integer ncclAllReduce over NVLink, unpack.
 // Integer sums are order-independent, so every rank holds bit-identical counts.
 int Sim::allreduce_charge() {
-    k_bbox_encode<<<1, 32, 0, stream>>>(st, d_bbox_red);
+    k_bbox_encode<<<1, 32, 0, stream>>>(st, d_bbox_red, cur);
     launches += 4;   // encode, decode, pack, unpack (NCCL's own kernels are not counted)
     int r = nccl->allReduce(d_bbox_red, d_bbox_red, 8, kNcclInt32, kNcclMax, comm, stream);
     if (r != 0) return fail(std::string("ncclAllReduce: ") + nccl->getErrorString(r), "Charge all-reduce");
-    k_bbox_decode<<<1, 32, 0, stream>>>(st, d_bbox_red);
+    k_bbox_decode<<<1, 32, 0, stream>>>(st, d_bbox_red, cur);
     CK(cudaMemcpyAsync(h_bbox_red, d_bbox_red, 8 * sizeof(int), cudaMemcpyDeviceToHost, stream), "Charge all-reduce");
     CK(cudaStreamSynchronize(stream), "Charge all-reduce");
     const int lx = -h_bbox_red[0], ly = -h_bbox_red[1], lz = -h_bbox_red[2];
@@ -355,10 +386,10 @@ int Sim::allreduce_charge() {
         box_buf_cells = cells + cells / 4;
         CK(cudaMalloc(&box_buf, box_buf_cells * 4), "Charge all-reduce");
     }
-    k_pack_box<<<aux_blocks, 256, 0, stream>>>(charge, box_buf, lx, ly, lz, wx, wy, wz, 0);
+    k_pack_box<<<aux_blocks, 256, 0, stream>>>(grid[cur], box_buf, lx, ly, lz, wx, wy, wz, 0);
     r = nccl->allReduce(box_buf, box_buf, cells, kNcclInt32, kNcclSum, comm, stream);
     if (r != 0) return fail(std::string("ncclAllReduce: ") + nccl->getErrorString(r), "Charge all-reduce");
-    k_pack_box<<<aux_blocks, 256, 0, stream>>>(charge, box_buf, lx, ly, lz, wx, wy, wz, 1);
+    k_pack_box<<<aux_blocks, 256, 0, stream>>>(grid[cur], box_buf, lx, ly, lz, wx, wy, wz, 1);
     CK_LAST("Charge all-reduce");
     return 0;
 }
@@ -439,9 +470,42 @@ int Sim::op_step_end() {
     return 0;
 }
 
+// Modes 30/33: `steps` iterations of runPIC's loop (src/pic.cu:487-560) in one cooperative launch.
+// Several ranks: one step per launch, with the charge all-reduce in between.
+int Sim::fused_steps(int steps) {
+    if (!charge_valid) {                    // first step after init/upload: grid[cur] needs this population's deposit
+        if (op_clear() || op_deposit()) return 1;
+    }
+    const int per_launch = cfg.nranks > 1 ? 1 : steps;
+    for (int done = 0; done < steps; done += per_launch) {
+        if (op_mobility_begin()) return 1;
+        FusedArgs a{soa, st, tables, {grid[0], grid[1]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed};
+        void* args[] = {&a};
+        span_begin(kPhMover);
+        CK(cudaLaunchCooperativeKernel((const void*)k_poisson_fused, dim3((unsigned)sm_count), dim3((unsigned)mover_threads), args,
+                                       (size_t)kFusedSmemBytes(mover_threads), stream),
+           "Mobility steps");
+        ++launches; ++mover_launches;
+        span_end();
+        if (cfg.nranks > 1) {               // the kernel deposited this rank's survivors into the other grid
+            cur ^= 1;
+            span_begin(kPhCollective);
+            const int rc = allreduce_charge();
+            span_end();
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
 // One iteration of runPIC's loop (src/pic.cu:487-560).
 int Sim::poisson_step(bool sync) {
     CK(cudaSetDevice(device), "Set device");
+    if (fused) {
+        if (fused_steps(1)) return 1;
+        return sync ? sync_state() : 0;
+    }
     if (op_deposit()) return 1;
     if (op_gather()) return 1;
     if (op_clear()) return 1;
@@ -578,9 +642,13 @@ int picb200_run_steps(picb200_sim* sim, int32_t steps) {
     CK(cudaSetDevice(s.device), "Set device");
     CK(cudaEventRecord(s.ev_start, s.stream), "Setup");
     const bool host_in_loop = s.cfg.mode == PICB200_MODE_CPU_SYNC || s.cfg.mode == PICB200_MODE_NAIVE || s.cfg.nranks > 1;
-    for (int t = 0; t < steps; ++t) {
-        if (s.poisson_step(false)) return 1;
-        if (host_in_loop && s.h_st->hit_zero) break;
+    if (s.fused) {
+        if (s.fused_steps(steps)) return 1;
+    } else {
+        for (int t = 0; t < steps; ++t) {
+            if (s.poisson_step(false)) return 1;
+            if (host_in_loop && s.h_st->hit_zero) break;
+        }
     }
     CK(cudaEventRecord(s.ev_stop, s.stream), "After sim");
     if (s.sync_state()) return 1;
@@ -633,7 +701,7 @@ int picb200_get_profile(picb200_sim* sim, picb200_profile* out) {
 int picb200_flush_l2(picb200_sim* sim) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
-    CK(cudaMemsetAsync(s.charge, 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
+    CK(cudaMemsetAsync(s.grid[s.cur ^ 1], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
     CK(cudaStreamSynchronize(s.stream), "Flush L2");
     return 0;
 }
@@ -653,7 +721,14 @@ int picb200_set_poisson_index(picb200_sim* sim, int32_t index) {
     return 0;
 }
 
-int picb200_op_deposit(picb200_sim* sim) { Sim& s = sim->s; cudaSetDevice(s.device); if (s.op_deposit()) return 1; return s.sync_state(); }
+int picb200_op_deposit(picb200_sim* sim) {
+    Sim& s = sim->s;
+    cudaSetDevice(s.device);
+    if (s.sync_state()) return 1;
+    if (s.charge_valid && s.op_clear()) return 1;     // e.g. after a fused step, which leaves the next deposit in place
+    if (s.op_deposit()) return 1;
+    return s.sync_state();
+}
 int picb200_op_gather(picb200_sim* sim) { Sim& s = sim->s; cudaSetDevice(s.device); if (s.op_gather()) return 1; return s.sync_state(); }
 int picb200_op_clear_grid(picb200_sim* sim) { Sim& s = sim->s; cudaSetDevice(s.device); if (s.op_clear()) return 1; return s.sync_state(); }
 int picb200_op_mobility(picb200_sim* sim) {
@@ -678,7 +753,7 @@ int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3
     int* buf = nullptr;
     const size_t cells = (size_t)wx * wy * wz;
     CK(cudaMalloc(&buf, cells * 4), "Charge box");
-    k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.charge, buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
+    k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.grid[s.cur], buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
     cudaError_t e = cudaMemcpyAsync(out, buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
     cudaFree(buf);
@@ -688,7 +763,7 @@ int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3
 int picb200_charge_bbox(picb200_sim* sim, int32_t lo[3], int32_t hi[3]) {
     Sim& s = sim->s;
     if (s.sync_state()) return 1;
-    for (int k = 0; k < 3; ++k) { lo[k] = s.h_st->bbox_lo[k]; hi[k] = s.h_st->bbox_hi[k]; }
+    for (int k = 0; k < 3; ++k) { lo[k] = s.h_st->bbox_lo[s.cur][k]; hi[k] = s.h_st->bbox_hi[s.cur][k]; }
     return 0;
 }
 

@@ -2,8 +2,8 @@
 //
 // K_mover: leapfrog + bounds + Monte-Carlo collision (updateParticle, src/particle_move.cu:22-87)
 // under the scheduling disciplines of src/pic.cu:
-//   kPersistent = true  (modes 30/33): ONE cooperative launch per Poisson step.  Warps claim
-//       32-electron chunks of the population with a ticket counter; an electron stays in
+//   kPersistent = true  (modes 30/33): ONE cooperative launch per Poisson step.  32-electron
+//       chunks of the population are dealt round-robin to the grid's warps; an electron stays in
 //       registers for all its remaining mobility steps.  Children are ranked into a warp-private
 //       stage in shared memory and the SAME warp later pushes them to the end of the Poisson step
 //       straight out of that stage, so a child normally reaches the global store exactly once, in
@@ -267,14 +267,11 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     if (kPersistent) {
         const int n0 = min(a.st->n, c.cap);
         const int chunks = (n0 + 31) >> 5;
-        // generation 0: chunks are claimed with a ticket; the next ticket is requested before the
-        // current chunk is processed so its latency hides behind the pushes
-        int next = 0;
-        if (c.lane == 0) next = atomicAdd(&a.st->ticket, 1);
-        for (;;) {
-            const int chunk = __shfl_sync(kFull, next, 0);
-            if (chunk >= chunks) break;
-            if (c.lane == 0) next = atomicAdd(&a.st->ticket, 1);
+        // generation 0: 32-electron chunks dealt round-robin over the grid's warps, SM-interleaved
+        // (warp w of block b is global warp w*gridDim+b), so every SM gets the same number of
+        // chunks to within one and no work counter is needed
+        const int gw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x, nw = gridDim.x * (blockDim.x >> 5);
+        for (int chunk = gw; chunk < chunks; chunk += nw) {
             process_chunk<true, false>(c, chunk << 5, n0, 1, c.pt, staged, pushes, dead);
             if (staged >= kDrainThreshold) process_staged(c, staged, pushes, dead);
         }
@@ -308,5 +305,275 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     if (c.lane == 0) {
         if (pushes) atomicAdd(&a.st->pushes, (unsigned long long)pushes);
         if (dead) atomicAdd(&a.st->n_dead, dead);
+    }
+}
+
+// =============================================================================================
+// K_poisson_fused (modes 30/33, the headline path): whole Poisson steps in ONE cooperative launch.
+// Per step, inside the kernel:
+//   generation 0   each claimed chunk gathers its field from charge grid A (updateGrid +
+//                  gridToParticles fused, src/grid_operations.cu:29-72), runs all mobility steps
+//                  (src/particle_move.cu:22-87), and deposits its survivors into charge grid B
+//                  (particlesToGrid of the NEXT step, src/grid_operations.cu:15-26);
+//   children       pushed out of the warp's stage, then deposited and stored once;
+//   barrier 1      (+ fall-back pass for spilled children, normally none)
+//   clear A        (resetGrid restricted to A's bounding box) + list holes/movers
+//   barrier 2      compaction moves (remove_dead_particles, src/pic.cu:320-357)
+//   barrier 3      the last block to arrive does the host's bookkeeping (src/pic.cu:539-559) and
+//                  swaps the roles of the two grids.
+// The reference needs 6 kernels, 3 memsets, 1 H2D and 2 blocking D2H copies for the same work
+// (src/pic.cu:495-553); here the host enqueues one kernel for any number of Poisson steps.
+// =============================================================================================
+struct FusedArgs {
+    Soa s;
+    DevState* st;
+    const float* tables;      // collision tables + cell boundary table
+    int* grid[2];
+    int* holes;
+    int* movers;
+    StepLog* log;
+    int log_len;
+    int capacity, pt, steps, stop_at_zero;
+    double efc;
+    uint2 seed;
+};
+
+// Exact cell index without the fp64 divide of src/grid_operations.cu:21-23: estimate with one fp32
+// multiply, then correct against bnd[k] = smallest fp32 x with trunc(double(x)/1e-2) >= k
+// (bnd[0] = -inf, bnd[512] = +inf, built on the host; checked for every fp32 in the domain by
+// tests/tools/check_cell_index.cpp).  Clamped to the grid like cell_of().
+constexpr int kBndBytes = (kGrid + 1) * 4;
+__device__ __forceinline__ int cell_of_fast(float p, const float* __restrict__ bnd) {
+    int k = __float2int_rz(__fmul_rn(p, 100.0f));
+    k = max(0, min(k, kGrid - 1));
+    k -= (p < bnd[k]) ? 1 : 0;
+    k += (p >= bnd[k + 1]) ? 1 : 0;
+    return k;
+}
+
+// NGP deposit of the active lanes with warp-level pre-reduction (lanes that hit the same cell
+// are merged into one red.global.add) and a block-level bounding box in shared memory.
+__device__ __forceinline__ void deposit_lanes(int* __restrict__ grid, bool active, int ix, int iy, int iz, int lane, int* s_box) {
+    const unsigned cell = active ? (unsigned)cell_index(ix, iy, iz) : (0xffffffffu - (unsigned)lane);
+    const unsigned peers = __match_any_sync(kFull, cell);
+    if (active && lane == __ffs(peers) - 1) atomicAdd(grid + cell, __popc(peers));
+    const int lx = __reduce_min_sync(kFull, active ? ix : kGrid), ly = __reduce_min_sync(kFull, active ? iy : kGrid),
+              lz = __reduce_min_sync(kFull, active ? iz : kGrid);
+    const int hx = __reduce_max_sync(kFull, active ? ix : -1), hy = __reduce_max_sync(kFull, active ? iy : -1),
+              hz = __reduce_max_sync(kFull, active ? iz : -1);
+    if (lane == 0 && hx >= 0) {
+        if (lx < s_box[0]) atomicMin(&s_box[0], lx);
+        if (ly < s_box[1]) atomicMin(&s_box[1], ly);
+        if (lz < s_box[2]) atomicMin(&s_box[2], lz);
+        if (hx > s_box[3]) atomicMax(&s_box[3], hx);
+        if (hy > s_box[4]) atomicMax(&s_box[4], hy);
+        if (hz > s_box[5]) atomicMax(&s_box[5], hz);
+    }
+}
+
+// Grid-wide barrier; the last block to arrive runs `action` (one thread) before everyone is released.
+template <class F>
+__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned target = (seq + 1u) * gridDim.x;
+        const unsigned prev = atomicAdd(&st->bar_count, 1u);
+        if (prev + 1u == target) {
+            __threadfence();
+            action();
+            __threadfence();
+            atomicExch(&st->bar_release, seq + 1u);
+        } else {
+            while (ld_acquire_u32(&st->bar_release) < seq + 1u) __nanosleep(32);
+        }
+        __threadfence();
+    }
+    ++seq;
+    __syncthreads();
+}
+
+struct FusedCtx {
+    const float* bnd;
+    int* A;
+    int* B;
+    int* s_box;
+    double efc;
+};
+
+// generation-0 chunk of the fused kernel: gather from A, push, deposit into B
+template <bool kLaterGen>
+__device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead) {
+    const int i = i0 + c.lane;
+    const bool in = i < end;
+    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int ts = kDead;
+    if (in) {
+        e.x = __ldcg(c.s.x + i); e.y = __ldcg(c.s.y + i); e.z = __ldcg(c.s.z + i);
+        e.vx = __ldcg(c.s.vx + i); e.vy = __ldcg(c.s.vy + i); e.vz = __ldcg(c.s.vz + i);
+        ts = __ldcg(c.s.ts + i);
+        e.id = __ldcg(c.s.id + i);
+        if (kLaterGen) { e.ax = __ldcg(c.s.ax + i); e.ay = __ldcg(c.s.ay + i); e.az = __ldcg(c.s.az + i); }
+    }
+    const bool was_alive = in && (kLaterGen ? ts >= 0 : ts != kDead);
+    if (!kLaterGen && was_alive) {
+        // updateGrid + gridToParticles for this electron's own cell (src/grid_operations.cu:29-72)
+        const int ix = cell_of_fast(e.x, f.bnd), iy = cell_of_fast(e.y, f.bnd), iz = cell_of_fast(e.z, f.bnd);
+        const int* q = f.A + cell_index(ix, iy, iz);
+        const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
+        const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
+        const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
+        e.ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
+        e.ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
+        e.az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
+        __stcg(c.s.ax + i, e.ax); __stcg(c.s.ay + i, e.ay); __stcg(c.s.az + i, e.az);
+    }
+    bool alive = was_alive;
+    const int t0 = max(1, ts + 1);          // src/pic.cu:218
+    bool touched = false;
+    advance<true>(c, e, alive, t0, c.pt, staged, pushes, dead, touched);
+    if (was_alive) {
+        if (touched) {
+            __stcg(c.s.x + i, e.x); __stcg(c.s.y + i, e.y); __stcg(c.s.z + i, e.z);
+            __stcg(c.s.vx + i, e.vx); __stcg(c.s.vy + i, e.vy); __stcg(c.s.vz + i, e.vz);
+        }
+        const int ts1 = alive ? -1 : kDead;
+        if (ts1 != ts) __stcg(c.s.ts + i, ts1);
+    }
+    deposit_lanes(f.B, alive, cell_of_fast(e.x, f.bnd), cell_of_fast(e.y, f.bnd), cell_of_fast(e.z, f.bnd), c.lane, f.s_box);
+}
+
+// children out of the warp's stage: push, deposit, store once (see process_staged)
+__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead) {
+    const int k = staged;
+    __syncwarp();
+    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int tb = 0;
+    if (c.lane < k) {
+        const uint32_t* g = c.stage + c.lane;
+        e.x = __uint_as_float(g[0 * 32]); e.y = __uint_as_float(g[1 * 32]); e.z = __uint_as_float(g[2 * 32]);
+        e.vx = __uint_as_float(g[3 * 32]); e.vy = __uint_as_float(g[4 * 32]); e.vz = __uint_as_float(g[5 * 32]);
+        e.ax = __uint_as_float(g[6 * 32]); e.ay = __uint_as_float(g[7 * 32]); e.az = __uint_as_float(g[8 * 32]);
+        tb = (int)g[9 * 32];
+        e.id = ((unsigned long long)g[11 * 32] << 32) | g[10 * 32];
+    }
+    staged = 0;
+    __syncwarp();
+    const int slot = reserve_slots(c, k) + c.lane;
+    const bool in = c.lane < k && slot < c.cap;
+    bool alive = in;
+    bool touched = false;
+    advance<true>(c, e, alive, tb + 1, c.pt, staged, pushes, dead, touched);
+    if (in) {
+        __stcg(c.s.x + slot, e.x); __stcg(c.s.y + slot, e.y); __stcg(c.s.z + slot, e.z);
+        __stcg(c.s.vx + slot, e.vx); __stcg(c.s.vy + slot, e.vy); __stcg(c.s.vz + slot, e.vz);
+        __stcg(c.s.ax + slot, e.ax); __stcg(c.s.ay + slot, e.ay); __stcg(c.s.az + slot, e.az);
+        __stcg(c.s.ts + slot, alive ? -1 : kDead);
+        __stcg(c.s.id + slot, e.id);
+    }
+    deposit_lanes(f.B, alive, cell_of_fast(e.x, f.bnd), cell_of_fast(e.y, f.bnd), cell_of_fast(e.z, f.bnd), c.lane, f.s_box);
+}
+
+constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
+constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
+constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * kStageBytesPerWarp; }
+
+__global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int s_box[6];
+    {
+        const float4* src = reinterpret_cast<const float4*>(a.tables);
+        float4* dst = reinterpret_cast<float4*>(smem_raw);
+        for (int k = threadIdx.x; k < kAllTableBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
+    }
+    if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
+    __syncthreads();
+
+    DevState* st = a.st;
+    MoverCtx c;
+    c.s = a.s;
+    c.st = st;
+    c.thr = reinterpret_cast<const float2*>(smem_raw);
+    c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
+    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kAllTableBytes) + (threadIdx.x >> 5) * (kStageWords * 32);
+    c.cap = a.capacity;
+    c.pt = a.pt;
+    c.lane = threadIdx.x & 31;
+    c.stepwise = 0;
+    c.seed = a.seed;
+    FusedCtx f;
+    f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
+    f.s_box = s_box;
+    f.efc = a.efc;
+
+    unsigned seq = 0;
+    for (int step = 0; step < a.steps; ++step) {
+        if (ld_volatile_i32(&st->hit_zero)) break;          // uniform: set before the previous barrier 3 released
+        const int cur = ld_volatile_i32(&st->cur);
+        f.A = a.grid[cur];
+        f.B = a.grid[cur ^ 1];
+        c.g0 = (unsigned)ld_volatile_i32(&st->poisson_index) * (unsigned)a.pt;
+        const int n0 = min(ld_volatile_i32(&st->n), c.cap);
+        const int chunks = (n0 + 31) >> 5;
+        int staged = 0;
+        unsigned pushes = 0;
+        int dead = 0;
+
+        // ---- generation 0 (+ this warp's own children): chunks dealt round-robin, SM-interleaved
+        const int gw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x, nw = gridDim.x * (blockDim.x >> 5);
+        for (int chunk = gw; chunk < chunks; chunk += nw) {
+            fused_chunk<false>(c, f, chunk << 5, n0, staged, pushes, dead);
+            if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
+        }
+        while (staged) fused_staged(c, f, staged, pushes, dead);
+
+        // ---- barrier 1 (+ fall-back passes over spilled children)
+        int lo = n0;
+        for (;;) {
+            for (int o = 16; o > 0; o >>= 1) {
+                pushes += __shfl_down_sync(kFull, pushes, o);
+                dead += __shfl_down_sync(kFull, dead, o);
+            }
+            if (c.lane == 0) {
+                if (pushes) atomicAdd(&st->pushes, (unsigned long long)pushes);
+                if (dead) atomicAdd(&st->n_dead, dead);
+            }
+            pushes = 0; dead = 0;
+            __syncthreads();
+            if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
+                atomicMin(&st->bbox_lo[cur ^ 1][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[cur ^ 1][threadIdx.x], s_box[3 + threadIdx.x]);
+            }
+            grid_barrier(st, seq, [&]() {
+                const int unfinished = ld_volatile_i32(&st->n_unfinished);
+                st->n_unfinished = 0;
+                st->gen_hi = unfinished > 0 ? min(ld_volatile_i32(&st->n_alloc), c.cap) : -1;
+            });
+            const int hi = ld_volatile_i32(&st->gen_hi);
+            if (hi < 0) break;
+            const int rounded = (hi - lo + 31) & ~31;
+            for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x) {
+                fused_chunk<true>(c, f, lo + k, hi, staged, pushes, dead);
+                if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
+            }
+            while (staged) fused_staged(c, f, staged, pushes, dead);
+            lo = hi;
+        }
+
+        // ---- every gather of this step is done: empty grid A; list the holes and movers
+        clear_box_body(st, f.A, cur);
+        compact_scan_body(c.s, st, c.cap, a.holes, a.movers);
+        grid_barrier(st, seq, []() {});
+        compact_move_body(c.s, st, a.holes, a.movers);
+        if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
+        // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
+        grid_barrier(st, seq, [&]() {
+            step_end_body(st, c.cap, a.log, a.log_len, a.stop_at_zero);
+            volatile DevState* v = st;
+            for (int k = 0; k < 3; ++k) { v->bbox_lo[cur][k] = kGrid; v->bbox_hi[cur][k] = -1; }
+            v->cur = cur ^ 1;
+            v->ticket = 0;
+            v->n_unfinished = 0;
+        });
     }
 }

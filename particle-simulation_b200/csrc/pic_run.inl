@@ -67,7 +67,8 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
         if (verbose && cfg.mode == PICB200_MODE_NAIVE) { s.naive_hook = naive_step_logger; s.naive_hook_user = sim; }
         if (!host_in_loop) {
             // modes 30/33: the whole run is enqueued; the host reads nothing until the end
-            for (int t = 0; t < P && !failed; ++t) failed = s.poisson_step(false) != 0;
+            if (s.fused) failed = s.fused_steps(P) != 0;
+            else for (int t = 0; t < P && !failed; ++t) failed = s.poisson_step(false) != 0;
             if (failed) break;
             std::vector<StepLog> lg((size_t)std::max(1, P));
             if (cudaMemcpyAsync(lg.data(), s.log, sizeof(StepLog) * (size_t)std::max(1, P), cudaMemcpyDeviceToHost, s.stream) != cudaSuccess ||
