@@ -480,7 +480,14 @@ int Sim::fused_steps(int steps) {
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
         FusedArgs a{soa, st, tables, {grid[0], grid[1]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
-                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed};
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr};
+        // PICB200_TRACE=<file>: dump 8 globaltimer stamps per block per Poisson step of this launch (debugging aid)
+        const char* trace_path = getenv("PICB200_TRACE");
+        const size_t trace_words = (size_t)per_launch * (size_t)sm_count * 8;
+        if (trace_path) {
+            CK(cudaMalloc(&a.trace, trace_words * 8), "Trace alloc");
+            CK(cudaMemsetAsync(a.trace, 0, trace_words * 8, stream), "Trace alloc");
+        }
         void* args[] = {&a};
         span_begin(kPhMover);
         CK(cudaLaunchCooperativeKernel((const void*)k_poisson_fused, dim3((unsigned)sm_count), dim3((unsigned)mover_threads), args,
@@ -488,6 +495,18 @@ int Sim::fused_steps(int steps) {
            "Mobility steps");
         ++launches; ++mover_launches;
         span_end();
+        if (trace_path) {
+            std::vector<unsigned long long> h(trace_words);
+            CK(cudaMemcpyAsync(h.data(), a.trace, trace_words * 8, cudaMemcpyDeviceToHost, stream), "Trace readback");
+            CK(cudaStreamSynchronize(stream), "Trace readback");
+            cudaFree(a.trace);
+            if (FILE* f = fopen(trace_path, "wb")) {
+                const int hdr[2] = {per_launch, sm_count};
+                fwrite(hdr, sizeof(int), 2, f);
+                fwrite(h.data(), 8, trace_words, f);
+                fclose(f);
+            }
+        }
         if (cfg.nranks > 1) {               // the kernel deposited this rank's survivors into the other grid
             cur ^= 1;
             span_begin(kPhCollective);

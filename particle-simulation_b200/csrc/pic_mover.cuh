@@ -336,7 +336,18 @@ struct FusedArgs {
     int capacity, pt, steps, stop_at_zero;
     double efc;
     uint2 seed;
+    unsigned long long* trace;   // optional (PICB200_TRACE): 8 globaltimer stamps per block per Poisson step
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define PIC_TRACE(slot)                                                                             \
+    do {                                                                                            \
+        if (a.trace && threadIdx.x == 0) a.trace[((size_t)step * gridDim.x + blockIdx.x) * 8 + (slot)] = globaltimer_ns(); \
+    } while (0)
 
 // Exact cell index without the fp64 divide of src/grid_operations.cu:21-23: estimate with one fp32
 // multiply, then correct against bnd[k] = smallest fp32 x with trunc(double(x)/1e-2) >= k
@@ -518,6 +529,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         int staged = 0;
         unsigned pushes = 0;
         int dead = 0;
+        PIC_TRACE(0);
 
         // ---- generation 0 (+ this warp's own children): chunks dealt round-robin, SM-interleaved
         const int gw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x, nw = gridDim.x * (blockDim.x >> 5);
@@ -526,6 +538,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
         }
         while (staged) fused_staged(c, f, staged, pushes, dead);
+        PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
         // ---- barrier 1 (+ fall-back passes over spilled children)
         int lo = n0;
@@ -540,6 +553,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             }
             pushes = 0; dead = 0;
             __syncthreads();
+            PIC_TRACE(2);      // every warp of the block finished
             if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
                 atomicMin(&st->bbox_lo[cur ^ 1][threadIdx.x], s_box[threadIdx.x]);
                 atomicMax(&st->bbox_hi[cur ^ 1][threadIdx.x], s_box[3 + threadIdx.x]);
@@ -561,11 +575,15 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         }
 
         // ---- every gather of this step is done: empty grid A; list the holes and movers
+        PIC_TRACE(3);          // barrier 1 passed
         clear_box_body(st, f.A, cur);
         compact_scan_body(c.s, st, c.cap, a.holes, a.movers);
+        PIC_TRACE(4);
         grid_barrier(st, seq, []() {});
+        PIC_TRACE(5);
         compact_move_body(c.s, st, a.holes, a.movers);
         if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
+        PIC_TRACE(6);
         // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
         grid_barrier(st, seq, [&]() {
             step_end_body(st, c.cap, a.log, a.log_len, a.stop_at_zero);
@@ -575,5 +593,6 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             v->ticket = 0;
             v->n_unfinished = 0;
         });
+        PIC_TRACE(7);
     }
 }

@@ -30,8 +30,8 @@ EXE = os.path.join(REF_DIR, "main")
 OUT = os.path.join(ROOT, "gpurun_out", "golden")
 TRANS = str.maketrans("():,[]", "      ")
 
-ENERGY_EDGES = np.linspace(-12.0, 0.0, 49)         # log10(|v|^2) bins
-OCC_MAX = 40
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from golden_stats import state_stats as _state_stats  # noqa: E402  (one binning for fixture and tests)
 
 
 def run_ref(args, timeout=1200):
@@ -71,25 +71,7 @@ def parse_dumps(txt):
 
 def state_stats(a):
     """Histograms of one state dump (rows: idx, x y z, vx vy vz, ax ay az, ts)."""
-    pos, vel = a[:, 1:4], a[:, 4:7]
-    e = (vel ** 2).sum(axis=1)
-    with np.errstate(divide="ignore"):
-        le = np.where(e > 0, np.log10(e), -np.inf)
-    eh, _ = np.histogram(le, bins=ENERGY_EDGES)
-    cells = (pos / 1e-2).astype(np.int64)
-    lin = (cells[:, 2] * 512 + cells[:, 1]) * 512 + cells[:, 0]
-    _, counts = np.unique(lin, return_counts=True)
-    occ = np.bincount(np.minimum(counts, OCC_MAX), minlength=OCC_MAX + 1)
-    return {
-        "n": int(a.shape[0]),
-        "energy_log10_edges": ENERGY_EDGES.tolist(), "energy_hist": eh.tolist(), "energy_below": int((le < ENERGY_EDGES[0]).sum()),
-        "energy_above": int((le >= ENERGY_EDGES[-1]).sum()),
-        "occupancy_hist": occ.tolist(), "occupied_cells": int(counts.size),
-        "v_mean": vel.mean(axis=0).tolist(), "v_rms": np.sqrt((vel ** 2).mean(axis=0)).tolist(),
-        "mean_energy": float(e.mean()), "median_energy": float(np.median(e)),
-        "pos_min": pos.min(axis=0).tolist(), "pos_max": pos.max(axis=0).tolist(),
-        "ts_all_minus1": bool(np.all(a[:, 10] == -1)),
-    }
+    return _state_stats(a[:, 1:4], a[:, 4:7], a[:, 10])
 
 
 def main():
