@@ -57,6 +57,13 @@ __device__ __forceinline__ int reserve_slots(const MoverCtx& c, int count) {
     return __shfl_sync(kFull, base, 0);
 }
 
+// A stage entry carries the parent's id and the birth step; the child's own id is derived when the
+// entry is consumed (all lanes busy) instead of when it is written (one or two lanes busy).
+__device__ __forceinline__ unsigned long long staged_child_id(const MoverCtx& c, const uint32_t* g) {
+    const unsigned long long parent = ((unsigned long long)g[11 * 32] << 32) | g[10 * 32];
+    return child_id(parent, (unsigned long long)(c.g0 + g[9 * 32]));
+}
+
 // Write the staged children to the global store as they are (timestamp = birth step): they still
 // need their remaining pushes.  kCount: tell the persistent kernel's fall-back pass they exist.
 template <bool kCount>
@@ -69,8 +76,9 @@ __device__ __forceinline__ void stage_spill(const MoverCtx& c, int count) {
         __stcg(c.s.x + slot, __uint_as_float(g[0 * 32])); __stcg(c.s.y + slot, __uint_as_float(g[1 * 32])); __stcg(c.s.z + slot, __uint_as_float(g[2 * 32]));
         __stcg(c.s.vx + slot, __uint_as_float(g[3 * 32])); __stcg(c.s.vy + slot, __uint_as_float(g[4 * 32])); __stcg(c.s.vz + slot, __uint_as_float(g[5 * 32]));
         __stcg(c.s.ax + slot, __uint_as_float(g[6 * 32])); __stcg(c.s.ay + slot, __uint_as_float(g[7 * 32])); __stcg(c.s.az + slot, __uint_as_float(g[8 * 32]));
-        __stcg(c.s.ts + slot, (int)g[9 * 32]);
-        __stcg(c.s.id + slot, ((unsigned long long)g[11 * 32] << 32) | g[10 * 32]);
+        const int tb = (int)g[9 * 32];
+        __stcg(c.s.ts + slot, (c.stepwise && tb == c.pt) ? -1 : tb);
+        __stcg(c.s.id + slot, staged_child_id(c, g));
     }
     if (kCount) {
         const unsigned m = __ballot_sync(kFull, w);
@@ -132,12 +140,11 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
             if (staged + cnt > 32) { stage_spill<kCountSpill>(c, staged); staged = 0; }
             if (spawn) {
                 uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
-                const unsigned long long cid = child_id(e.id, (unsigned long long)g);
                 q[0 * 32] = __float_as_uint(e.x); q[1 * 32] = __float_as_uint(e.y); q[2 * 32] = __float_as_uint(e.z);
                 q[3 * 32] = __float_as_uint(cvx); q[4 * 32] = __float_as_uint(cvy); q[5 * 32] = __float_as_uint(cvz);
                 q[6 * 32] = __float_as_uint(e.ax); q[7 * 32] = __float_as_uint(e.ay); q[8 * 32] = __float_as_uint(e.az);
-                q[9 * 32] = (uint32_t)((c.stepwise && t == c.pt) ? -1 : t);
-                q[10 * 32] = (uint32_t)cid; q[11 * 32] = (uint32_t)(cid >> 32);
+                q[9 * 32] = (uint32_t)t;
+                q[10 * 32] = (uint32_t)e.id; q[11 * 32] = (uint32_t)(e.id >> 32);
             }
             staged += cnt;
         }
@@ -193,7 +200,7 @@ __device__ __forceinline__ void process_staged(const MoverCtx& c, int& staged, u
         e.vx = __uint_as_float(g[3 * 32]); e.vy = __uint_as_float(g[4 * 32]); e.vz = __uint_as_float(g[5 * 32]);
         e.ax = __uint_as_float(g[6 * 32]); e.ay = __uint_as_float(g[7 * 32]); e.az = __uint_as_float(g[8 * 32]);
         tb = (int)g[9 * 32];
-        e.id = ((unsigned long long)g[11 * 32] << 32) | g[10 * 32];
+        e.id = staged_child_id(c, g);
     }
     staged = 0;
     __syncwarp();
@@ -410,6 +417,7 @@ struct FusedCtx {
     int* B;
     int* s_box;
     double efc;
+    bool store_acc;   // last Poisson step of this launch: the frozen acceleration becomes visible to the host
 };
 
 // generation-0 chunk of the fused kernel: gather from A, push, deposit into B
@@ -437,7 +445,7 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
         e.ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
         e.ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
         e.az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
-        __stcg(c.s.ax + i, e.ax); __stcg(c.s.ay + i, e.ay); __stcg(c.s.az + i, e.az);
+        if (f.store_acc) { __stcg(c.s.ax + i, e.ax); __stcg(c.s.ay + i, e.ay); __stcg(c.s.az + i, e.az); }
     }
     bool alive = was_alive;
     const int t0 = max(1, ts + 1);          // src/pic.cu:218
@@ -454,6 +462,103 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
     deposit_lanes(f.B, alive, cell_of_fast(e.x, f.bnd), cell_of_fast(e.y, f.bnd), cell_of_fast(e.z, f.bnd), c.lane, f.s_box);
 }
 
+
+// The common case of the fused kernel: a chunk whose 32 electrons are all "alive since the start of
+// the Poisson step" (ts == -1; anything else takes fused_chunk<false>).  All lanes then run the same
+// mobility step t, so the step loop is straight-line code: the Philox block changes for the whole
+// warp at once, dead lanes keep computing values nobody stores instead of branching around the body,
+// and the only branch is the warp vote "somebody spawned".
+__device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead) {
+    const int i = i0 + c.lane;
+    const bool in = i < end;
+    float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f;
+    unsigned long long id = 0;
+    int ts = -1;
+    if (in) {
+        x = __ldcg(c.s.x + i); y = __ldcg(c.s.y + i); z = __ldcg(c.s.z + i);
+        vx = __ldcg(c.s.vx + i); vy = __ldcg(c.s.vy + i); vz = __ldcg(c.s.vz + i);
+        ts = __ldcg(c.s.ts + i);
+        id = __ldcg(c.s.id + i);
+    }
+    if (__any_sync(kFull, ts != -1)) {          // uploaded populations may carry other timestamps
+        fused_chunk<false>(c, f, i0, end, staged, pushes, dead);
+        return;
+    }
+    // updateGrid + gridToParticles for this electron's own cell (src/grid_operations.cu:29-72)
+    float ax = 0.f, ay = 0.f, az = 0.f;
+    const float x0 = x, y0 = y, z0 = z;
+    int ix = cell_of_fast(x, f.bnd), iy = cell_of_fast(y, f.bnd), iz = cell_of_fast(z, f.bnd);
+    if (in) {
+        const int* q = f.A + cell_index(ix, iy, iz);
+        const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
+        const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
+        const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
+        ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
+        ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
+        az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
+        if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
+    }
+    const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
+    const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
+    bool alive = in;
+    unsigned g = c.g0;
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+    for (int t = 1; t <= c.pt; ++t) {
+        ++g;
+        if (t == 1 || (g & 3u) == 0u)                            // warp-uniform
+            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), c.seed);
+        // leapfrog, src/particle_move.cu:22-39
+        vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
+        x = __fmaf_rn(vx, dt, x); y = __fmaf_rn(vy, dt, y); z = __fmaf_rn(vz, dt, z);
+        vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
+        // checkOutOfBounds, src/particle_move.cu:41-52 (a NaN coordinate is NOT out of bounds)
+        const bool oob = (x < 0.f) | (x >= sim) | (y < 0.f) | (y >= sim) | (z < 0.f) | (z >= sim);
+        // collider, src/particle_move.cu:55-80
+        const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
+        const float r = __fmul_rn(uniform01((g & 2u) ? w23 : w01), 100.0f);
+        const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
+        const float2 th = c.thr[energy_index(en, c.edge)];
+        const bool coll = alive & !oob;
+        const bool spawn = coll & (r < th.x);                    // ionisation
+        const bool die = alive & (oob | (!spawn & (r < th.y)));  // left the domain, or attachment
+        pushes += alive ? 1u : 0u;
+        const unsigned m = __ballot_sync(kFull, spawn);
+        if (m) {
+            const int cnt = __popc(m);
+            if (staged + cnt > 32) { stage_spill<true>(c, staged); staged = 0; }
+            if (spawn) {                                         // the child copies the pre-flip state
+                uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
+                q[0 * 32] = __float_as_uint(x); q[1 * 32] = __float_as_uint(y); q[2 * 32] = __float_as_uint(z);
+                q[3 * 32] = __float_as_uint(vx); q[4 * 32] = __float_as_uint(vy); q[5 * 32] = __float_as_uint(vz);
+                q[6 * 32] = __float_as_uint(ax); q[7 * 32] = __float_as_uint(ay); q[8 * 32] = __float_as_uint(az);
+                q[9 * 32] = (uint32_t)t;
+                q[10 * 32] = (uint32_t)id; q[11 * 32] = (uint32_t)(id >> 32);
+            }
+            staged += cnt;
+            const uint32_t flip = spawn ? 0x80000000u : 0u;      // parent v = -v
+            vx = __uint_as_float(__float_as_uint(vx) ^ flip);
+            vy = __uint_as_float(__float_as_uint(vy) ^ flip);
+            vz = __uint_as_float(__float_as_uint(vz) ^ flip);
+        }
+        dead += die ? 1 : 0;
+        alive = alive & !die;
+    }
+    if (in) {
+        if (alive) {
+            __stcg(c.s.x + i, x); __stcg(c.s.y + i, y); __stcg(c.s.z + i, z);
+            __stcg(c.s.vx + i, vx); __stcg(c.s.vy + i, vy); __stcg(c.s.vz + i, vz);
+        } else {
+            __stcg(c.s.ts + i, kDead);
+        }
+    }
+    // particlesToGrid of the next Poisson step; the cell is recomputed only where the coordinate changed
+    if (__any_sync(kFull, alive & ((x != x0) | (y != y0) | (z != z0)))) {
+        ix = cell_of_fast(x, f.bnd); iy = cell_of_fast(y, f.bnd); iz = cell_of_fast(z, f.bnd);
+    }
+    deposit_lanes(f.B, alive, ix, iy, iz, c.lane, f.s_box);
+}
+
 // children out of the warp's stage: push, deposit, store once (see process_staged)
 __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead) {
     const int k = staged;
@@ -466,7 +571,7 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
         e.vx = __uint_as_float(g[3 * 32]); e.vy = __uint_as_float(g[4 * 32]); e.vz = __uint_as_float(g[5 * 32]);
         e.ax = __uint_as_float(g[6 * 32]); e.ay = __uint_as_float(g[7 * 32]); e.az = __uint_as_float(g[8 * 32]);
         tb = (int)g[9 * 32];
-        e.id = ((unsigned long long)g[11 * 32] << 32) | g[10 * 32];
+        e.id = staged_child_id(c, g);
     }
     staged = 0;
     __syncwarp();
@@ -478,7 +583,7 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
     if (in) {
         __stcg(c.s.x + slot, e.x); __stcg(c.s.y + slot, e.y); __stcg(c.s.z + slot, e.z);
         __stcg(c.s.vx + slot, e.vx); __stcg(c.s.vy + slot, e.vy); __stcg(c.s.vz + slot, e.vz);
-        __stcg(c.s.ax + slot, e.ax); __stcg(c.s.ay + slot, e.ay); __stcg(c.s.az + slot, e.az);
+        if (f.store_acc) { __stcg(c.s.ax + slot, e.ax); __stcg(c.s.ay + slot, e.ay); __stcg(c.s.az + slot, e.az); }
         __stcg(c.s.ts + slot, alive ? -1 : kDead);
         __stcg(c.s.id + slot, e.id);
     }
@@ -533,8 +638,9 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
 
         // ---- generation 0 (+ this warp's own children): chunks dealt round-robin, SM-interleaved
         const int gw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x, nw = gridDim.x * (blockDim.x >> 5);
+        f.store_acc = step == a.steps - 1;
         for (int chunk = gw; chunk < chunks; chunk += nw) {
-            fused_chunk<false>(c, f, chunk << 5, n0, staged, pushes, dead);
+            fused_chunk_fast(c, f, chunk << 5, n0, staged, pushes, dead);
             if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
         }
         while (staged) fused_staged(c, f, staged, pushes, dead);
