@@ -17,6 +17,7 @@ namespace picb200 {
 constexpr int kGrid = 512;              // src/cell.cu:3
 constexpr int kRows = 10000;            // src/cross_section.h:9
 constexpr int kDead = -2;               // src/electron.h:8
+constexpr int kGrids = 3;               // charge grids in rotation (gather / next deposit / being emptied)
 constexpr unsigned kFull = 0xffffffffu;
 constexpr uint32_t kTagCollide = 0u, kTagInit = 1u;
 
@@ -41,8 +42,8 @@ struct DevState {
     int n_holes, n_movers;  // compaction work lists
     int gen_hi;             // end of the fall-back window agreed at the barrier (-1: none)
     int n_unfinished;       // children spilled to the global store before they were pushed to the end
-    int bbox_lo[2][3], bbox_hi[2][3];  // cell bounding box of the counts deposited in charge grid 0 / 1
-    int cur;                // which of the two charge grids holds the current deposit
+    int bbox_lo[kGrids][3], bbox_hi[kGrids][3];  // cell bounding box of the counts deposited in each charge grid
+    int cur;                // which of the charge grids holds the current deposit
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)
     int overflow_steps;     // steps whose n reached capacity (src/pic.cu:544)
@@ -217,27 +218,40 @@ __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ char
 }
 
 // K_clear: resetGrid (src/grid_operations.cu:6-12) restricted to the deposited bounding box.
+// Warp-granular form for the fused kernel: global warp `gw` of `nw` empties its x-rows of the box.
+__device__ __forceinline__ void clear_box_rows(const DevState* st, int* __restrict__ charge, int which, int gw, int nw, int lane) {
+    const int lx = __ldcg(&st->bbox_lo[which][0]), ly = __ldcg(&st->bbox_lo[which][1]), lz = __ldcg(&st->bbox_lo[which][2]);
+    const int wx = __ldcg(&st->bbox_hi[which][0]) - lx + 1, wy = __ldcg(&st->bbox_hi[which][1]) - ly + 1,
+              wz = __ldcg(&st->bbox_hi[which][2]) - lz + 1;
+    if (wx <= 0 || wy <= 0 || wz <= 0) return;
+    const int rows = wy * wz;
+    for (int r = gw; r < rows; r += nw) {
+        const int yy = r % wy, zz = r / wy;
+        int* row = charge + cell_index(lx, ly + yy, lz + zz);
+        for (int xx = lane; xx < wx; xx += 32) __stcg(row + xx, 0);
+    }
+}
 __device__ __forceinline__ void clear_box_body(const DevState* st, int* __restrict__ charge, int which) {
     const int lx = ld_volatile_i32(&st->bbox_lo[which][0]), ly = ld_volatile_i32(&st->bbox_lo[which][1]), lz = ld_volatile_i32(&st->bbox_lo[which][2]);
     const int wx = ld_volatile_i32(&st->bbox_hi[which][0]) - lx + 1, wy = ld_volatile_i32(&st->bbox_hi[which][1]) - ly + 1,
               wz = ld_volatile_i32(&st->bbox_hi[which][2]) - lz + 1;
     if (wx <= 0 || wy <= 0 || wz <= 0) return;
-    const long long total = (long long)wx * wy * wz;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
-        const int x = (int)(k % wx);
-        const long long r = k / wx;
-        const int y = (int)(r % wy), z = (int)(r / wy);
-        __stcg(charge + cell_index(lx + x, ly + y, lz + z), 0);
+    // one warp per x-row of the box: contiguous stores, no 64-bit division
+    const int lane = threadIdx.x & 31;
+    const int rows = wy * wz, nw = (gridDim.x * blockDim.x) >> 5;
+    for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows; r += nw) {
+        const int yy = r % wy, zz = r / wy;
+        int* row = charge + cell_index(lx, ly + yy, lz + zz);
+        for (int xx = lane; xx < wx; xx += 32) __stcg(row + xx, 0);
     }
 }
 __global__ void k_clear_box(const DevState* st, int* __restrict__ charge, int which) { clear_box_body(st, charge, which); }
 __global__ void k_set_n(DevState* st, int n) { st->n = n; st->n_alloc = n; }
-// which: 0 / 1 = that grid's box, 2 = both
+// which: 0 .. kGrids-1 = that grid's box, kGrids = all
 __global__ void k_reset_bbox(DevState* st, int which) {
-    if (threadIdx.x < 3) {
-        if (which != 1) { st->bbox_lo[0][threadIdx.x] = kGrid; st->bbox_hi[0][threadIdx.x] = -1; }
-        if (which != 0) { st->bbox_lo[1][threadIdx.x] = kGrid; st->bbox_hi[1][threadIdx.x] = -1; }
-    }
+    if (threadIdx.x < 3)
+        for (int g = 0; g < kGrids; ++g)
+            if (which == g || which == kGrids) { st->bbox_lo[g][threadIdx.x] = kGrid; st->bbox_hi[g][threadIdx.x] = -1; }
 }
 
 // Multi-GPU: the union bounding box is one max-reduction of {-lo[3], hi[3], 0, 0}.
@@ -268,11 +282,14 @@ __global__ void k_pack_box(const int* __restrict__ charge, int* __restrict__ buf
 // (warp-aggregated appends), pass 2 copies mover k into hole k.  Traffic is proportional to
 // the number of dead electrons, not to n, and no second capacity-sized buffer exists.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
-    // One pair of global atomics per BLOCK: every block owns a contiguous range of 32-slot groups,
-    // counts its holes and movers (pass 1), reserves list space once, and fills it (pass 2, the
-    // timestamps come from L2 the second time).  Per-warp atomics on the two list cursors
-    // serialised in L2 and cost 37 us per Poisson step at 1.2e6 slots.
+__device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers,
+                                                  unsigned long long* trace = nullptr) {
+    // Every block owns a contiguous range of 128-slot "quads" (one int4 of timestamps per lane).  A warp
+    // loads up to kScanDepth quads back to back (all loads in flight at once), keeps the hole / mover
+    // flags of its slots in two bit masks, and the block reserves list space with ONE pair of global
+    // atomics per round -- per-warp atomics on the two list cursors serialised in L2 and cost 37 us per
+    // Poisson step at 1.2e6 slots; re-reading the timestamps in a second pass cost another 8 us.
+    constexpr int kScanDepth = 8;
     __shared__ int s_cnt[2][32];
     __shared__ int s_base[2];
     const int S = min(ld_volatile_i32(&st->n_alloc), capacity);
@@ -280,51 +297,60 @@ __device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, in
     if (D == 0) return;                                       // uniform over the grid
     const int L = S - D;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int groups = (S + 31) >> 5;
-    const int per_block = (groups + gridDim.x - 1) / gridDim.x;
-    const int g_lo = min(groups, (int)blockIdx.x * per_block), g_hi = min(groups, g_lo + per_block);
-    int ch = 0, cm = 0;
-    for (int g = g_lo + warp; g < g_hi; g += nwarps) {
-        const int i = (g << 5) + lane;
-        const bool in = i < S;
-        const bool dead = in && __ldcg(s.ts + i) == kDead;
-        ch += __popc(__ballot_sync(kFull, dead && i < L));
-        cm += __popc(__ballot_sync(kFull, in && !dead && i >= L));
-    }
-    if (lane == 0) { s_cnt[0][warp] = ch; s_cnt[1][warp] = cm; }
-    __syncthreads();
-    if (warp == 0) {
-        const int vh = lane < nwarps ? s_cnt[0][lane] : 0, vm = lane < nwarps ? s_cnt[1][lane] : 0;
-        int ph = vh, pm = vm;                                 // inclusive scan over the warps of the block
+    const int quads = (S + 127) >> 7;
+    const int per_block = (quads + gridDim.x - 1) / gridDim.x;
+    const int q_lo = min(quads, (int)blockIdx.x * per_block), q_hi = min(quads, q_lo + per_block);
+    const int per_round = nwarps * kScanDepth;
+    for (int q0 = q_lo; q0 < q_hi; q0 += per_round) {         // uniform over the block
+        unsigned hm = 0, mm = 0;                              // bit 4k+j: slot j of this lane's int4 in quad k
+#pragma unroll
+        for (int k = 0; k < kScanDepth; ++k) {
+            const int q = q0 + warp * kScanDepth + k;
+            const int i = (q << 7) + (lane << 2);
+            if (q < q_hi && i < S) {                          // i + 3 stays inside the 256-byte padded array
+                const int4 t4 = __ldcg(reinterpret_cast<const int4*>(s.ts + i));
+                const int tv[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const bool in = i + j < S, dead = tv[j] == kDead;
+                    if (in && dead && i + j < L) hm |= 1u << (4 * k + j);
+                    if (in && !dead && i + j >= L) mm |= 1u << (4 * k + j);
+                }
+            }
+        }
+        const int ch = __popc(hm), cm = __popc(mm);
+        if (trace && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); trace[9] = t; }
+        int ph = ch, pm = cm;                                 // inclusive scan over the lanes of the warp
+#pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int th = __shfl_up_sync(kFull, ph, o), tm = __shfl_up_sync(kFull, pm, o);
             if (lane >= o) { ph += th; pm += tm; }
         }
-        const int tot_h = __shfl_sync(kFull, ph, 31), tot_m = __shfl_sync(kFull, pm, 31);
-        if (lane == 0) {
-            s_base[0] = tot_h ? atomicAdd(&st->n_holes, tot_h) : 0;
-            s_base[1] = tot_m ? atomicAdd(&st->n_movers, tot_m) : 0;
+        if (lane == 31) { s_cnt[0][warp] = ph; s_cnt[1][warp] = pm; }
+        __syncthreads();
+        if (warp == 0) {
+            const int vh = lane < nwarps ? s_cnt[0][lane] : 0, vm = lane < nwarps ? s_cnt[1][lane] : 0;
+            int wh = vh, wm = vm;                             // inclusive scan over the warps of the block
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int th = __shfl_up_sync(kFull, wh, o), tm = __shfl_up_sync(kFull, wm, o);
+                if (lane >= o) { wh += th; wm += tm; }
+            }
+            const int tot_h = __shfl_sync(kFull, wh, 31), tot_m = __shfl_sync(kFull, wm, 31);
+            if (lane == 0) {
+                s_base[0] = tot_h ? atomicAdd(&st->n_holes, tot_h) : 0;
+                s_base[1] = tot_m ? atomicAdd(&st->n_movers, tot_m) : 0;
+            }
+            if (lane < nwarps) { s_cnt[0][lane] = wh - vh; s_cnt[1][lane] = wm - vm; }
         }
-        if (lane < nwarps) { s_cnt[0][lane] = ph - vh; s_cnt[1][lane] = pm - vm; }
+        __syncthreads();
+        if (trace && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); trace[10] = t; }
+        int oh = s_base[0] + s_cnt[0][warp] + ph - ch, om = s_base[1] + s_cnt[1][warp] + pm - cm;
+        const int i_base = ((q0 + warp * kScanDepth) << 7) + (lane << 2);
+        while (hm) { const int b = __ffs(hm) - 1; hm &= hm - 1; __stcg(holes + oh++, i_base + ((b >> 2) << 7) + (b & 3)); }
+        while (mm) { const int b = __ffs(mm) - 1; mm &= mm - 1; __stcg(movers + om++, i_base + ((b >> 2) << 7) + (b & 3)); }
+        __syncthreads();                                      // s_cnt / s_base are reused by the next round
     }
-    __syncthreads();
-    int bh = s_base[0] + s_cnt[0][warp], bm = s_base[1] + s_cnt[1][warp];
-    if (ch | cm) {
-        for (int g = g_lo + warp; g < g_hi; g += nwarps) {
-            const int i = (g << 5) + lane;
-            const bool in = i < S;
-            const bool dead = in && __ldcg(s.ts + i) == kDead;
-            const bool is_hole = dead && i < L;
-            const bool is_mover = in && !dead && i >= L;
-            const unsigned mh = __ballot_sync(kFull, is_hole);
-            const unsigned mm = __ballot_sync(kFull, is_mover);
-            if (is_hole) __stcg(holes + bh + __popc(mh & lanemask_lt()), i);
-            if (is_mover) __stcg(movers + bm + __popc(mm & lanemask_lt()), i);
-            bh += __popc(mh);
-            bm += __popc(mm);
-        }
-    }
-    __syncthreads();                                          // s_cnt / s_base are reused by the next call
 }
 __global__ void k_compact_scan(Soa s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
     compact_scan_body(s, st, capacity, holes, movers);

@@ -93,7 +93,7 @@ struct Sim {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     Soa soa{};
     void* soa_base = nullptr;
-    int* grid[2] = {nullptr, nullptr};   // two charge grids: gather from one while the next deposit fills the other
+    int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
     int* holes = nullptr;
@@ -185,8 +185,7 @@ void Sim::release() {
     if (comm && nccl) { nccl->commDestroy(comm); comm = nullptr; }
     if (stream) { cudaStreamSynchronize(stream); }
     cudaFree(soa_base); soa_base = nullptr;
-    cudaFree(grid[0]); grid[0] = nullptr;
-    cudaFree(grid[1]); grid[1] = nullptr;
+    for (int g = 0; g < kGrids; ++g) { cudaFree(grid[g]); grid[g] = nullptr; }
     cudaFree(holes); holes = nullptr;
     cudaFree(movers); movers = nullptr;
     cudaFree(tables); tables = nullptr;
@@ -265,14 +264,14 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&movers, list_cap * 4), "Minor alloc");
 
     // ---- charge grid 512^3 int32, zeroed once (src/pic.cu:448-450 allocates 2 GiB of 16-B cells)
-    for (int g = 0; g < 2; ++g) {
+    for (int g = 0; g < kGrids; ++g) {
         CK(cudaMalloc(&grid[g], (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
         CK(cudaMemsetAsync(grid[g], 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
     }
 
     CK(cudaMalloc(&st, sizeof(DevState)), "Minor alloc");
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Minor alloc");
-    k_reset_bbox<<<1, 32, 0, stream>>>(st, 2);
+    k_reset_bbox<<<1, 32, 0, stream>>>(st, kGrids);
     CK(cudaMallocHost(&h_st, sizeof(DevState)), "Minor alloc");
     memset(h_st, 0, sizeof(DevState));
     log_len = std::max(1, cfg.poisson_steps);
@@ -310,10 +309,9 @@ int Sim::sync_state() {
 // A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
 int Sim::reset_state() {
     // a deposit of the previous population may still sit in either grid: both boxes bound it
-    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[0], 0);
-    k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[1], 1);
+    for (int g = 0; g < kGrids; ++g) k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[g], g);
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
-    k_reset_bbox<<<1, 32, 0, stream>>>(st, 2);
+    k_reset_bbox<<<1, 32, 0, stream>>>(st, kGrids);
     CK_LAST("Reset state");
     gpu_ms = 0;
     cur = 0;
@@ -479,11 +477,11 @@ int Sim::fused_steps(int steps) {
     const int per_launch = cfg.nranks > 1 ? 1 : steps;
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
-        FusedArgs a{soa, st, tables, {grid[0], grid[1]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
+        FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr};
-        // PICB200_TRACE=<file>: dump 8 globaltimer stamps per block per Poisson step of this launch (debugging aid)
+        // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
-        const size_t trace_words = (size_t)per_launch * (size_t)sm_count * 8;
+        const size_t trace_words = (size_t)per_launch * (size_t)sm_count * 16;
         if (trace_path) {
             CK(cudaMalloc(&a.trace, trace_words * 8), "Trace alloc");
             CK(cudaMemsetAsync(a.trace, 0, trace_words * 8, stream), "Trace alloc");
@@ -508,7 +506,7 @@ int Sim::fused_steps(int steps) {
             }
         }
         if (cfg.nranks > 1) {               // the kernel deposited this rank's survivors into the other grid
-            cur ^= 1;
+            cur = (cur + 1) % kGrids;
             span_begin(kPhCollective);
             const int rc = allreduce_charge();
             span_end();
@@ -720,7 +718,7 @@ int picb200_get_profile(picb200_sim* sim, picb200_profile* out) {
 int picb200_flush_l2(picb200_sim* sim) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
-    CK(cudaMemsetAsync(s.grid[s.cur ^ 1], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
+    CK(cudaMemsetAsync(s.grid[(s.cur + 1) % kGrids], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
     CK(cudaStreamSynchronize(s.stream), "Flush L2");
     return 0;
 }

@@ -335,7 +335,7 @@ struct FusedArgs {
     Soa s;
     DevState* st;
     const float* tables;      // collision tables + cell boundary table
-    int* grid[2];
+    int* grid[kGrids];
     int* holes;
     int* movers;
     StepLog* log;
@@ -343,7 +343,7 @@ struct FusedArgs {
     int capacity, pt, steps, stop_at_zero;
     double efc;
     uint2 seed;
-    unsigned long long* trace;   // optional (PICB200_TRACE): 8 globaltimer stamps per block per Poisson step
+    unsigned long long* trace;   // optional (PICB200_TRACE): 16 globaltimer stamps per block per Poisson step
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -353,7 +353,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 #define PIC_TRACE(slot)                                                                             \
     do {                                                                                            \
-        if (a.trace && threadIdx.x == 0) a.trace[((size_t)step * gridDim.x + blockIdx.x) * 8 + (slot)] = globaltimer_ns(); \
+        if (a.trace && threadIdx.x == 0) a.trace[((size_t)step * gridDim.x + blockIdx.x) * 16 + (slot)] = globaltimer_ns(); \
     } while (0)
 
 // Exact cell index without the fp64 divide of src/grid_operations.cu:21-23: estimate with one fp32
@@ -597,6 +597,10 @@ constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_box[6];
+    __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
+    __shared__ unsigned long long s_pushes;
+    __shared__ int s_dead;
+    if (threadIdx.x == 0) { s_ticket = 0; s_pushes = 0; s_dead = 0; }
     {
         const float4* src = reinterpret_cast<const float4*>(a.tables);
         float4* dst = reinterpret_cast<float4*>(smem_raw);
@@ -626,8 +630,10 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     for (int step = 0; step < a.steps; ++step) {
         if (ld_volatile_i32(&st->hit_zero)) break;          // uniform: set before the previous barrier 3 released
         const int cur = ld_volatile_i32(&st->cur);
-        f.A = a.grid[cur];
-        f.B = a.grid[cur ^ 1];
+        const int nxt = (cur + 1) % kGrids, old = (cur + 2) % kGrids;
+        f.A = a.grid[cur];       // gathered from
+        f.B = a.grid[nxt];       // receives the deposit of the next Poisson step
+                                 // a.grid[old] was gathered from one step ago and is emptied below
         c.g0 = (unsigned)ld_volatile_i32(&st->poisson_index) * (unsigned)a.pt;
         const int n0 = min(ld_volatile_i32(&st->n), c.cap);
         const int chunks = (n0 + 31) >> 5;
@@ -636,14 +642,22 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         int dead = 0;
         PIC_TRACE(0);
 
-        // ---- generation 0 (+ this warp's own children): chunks dealt round-robin, SM-interleaved
-        const int gw = (threadIdx.x >> 5) * gridDim.x + blockIdx.x, nw = gridDim.x * (blockDim.x >> 5);
+        // ---- generation 0 (+ this warp's own children): chunk k of block b is global chunk k*gridDim+b,
+        // so every SM gets the same number of chunks to within one; inside the block the warps draw
+        // their next chunk from a shared-memory ticket, which evens out the children they pick up
         f.store_acc = step == a.steps - 1;
-        for (int chunk = gw; chunk < chunks; chunk += nw) {
+        for (;;) {
+            int k = 0;
+            if (c.lane == 0) k = atomicAdd(&s_ticket, 1);
+            const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
+            if (chunk >= chunks) break;
             fused_chunk_fast(c, f, chunk << 5, n0, staged, pushes, dead);
             if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
         }
         while (staged) fused_staged(c, f, staged, pushes, dead);
+        // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
+        // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
+        clear_box_rows(st, a.grid[old], old, (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), (int)(gridDim.x * (blockDim.x >> 5)), c.lane);
         PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
         // ---- barrier 1 (+ fall-back passes over spilled children)
@@ -653,16 +667,21 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 pushes += __shfl_down_sync(kFull, pushes, o);
                 dead += __shfl_down_sync(kFull, dead, o);
             }
-            if (c.lane == 0) {
-                if (pushes) atomicAdd(&st->pushes, (unsigned long long)pushes);
-                if (dead) atomicAdd(&st->n_dead, dead);
+            if (c.lane == 0) {                                   // one global atomic per block, not per warp
+                if (pushes) atomicAdd(&s_pushes, (unsigned long long)pushes);
+                if (dead) atomicAdd(&s_dead, dead);
             }
             pushes = 0; dead = 0;
             __syncthreads();
             PIC_TRACE(2);      // every warp of the block finished
+            if (threadIdx.x == 32) {
+                if (s_pushes) atomicAdd(&st->pushes, s_pushes);
+                if (s_dead) atomicAdd(&st->n_dead, s_dead);
+                s_pushes = 0; s_dead = 0;
+            }
             if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
-                atomicMin(&st->bbox_lo[cur ^ 1][threadIdx.x], s_box[threadIdx.x]);
-                atomicMax(&st->bbox_hi[cur ^ 1][threadIdx.x], s_box[3 + threadIdx.x]);
+                atomicMin(&st->bbox_lo[nxt][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[nxt][threadIdx.x], s_box[3 + threadIdx.x]);
             }
             grid_barrier(st, seq, [&]() {
                 const int unfinished = ld_volatile_i32(&st->n_unfinished);
@@ -680,22 +699,23 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             lo = hi;
         }
 
-        // ---- every gather of this step is done: empty grid A; list the holes and movers
+        // ---- every push of this step is done: list the holes and movers
         PIC_TRACE(3);          // barrier 1 passed
-        clear_box_body(st, f.A, cur);
-        compact_scan_body(c.s, st, c.cap, a.holes, a.movers);
+        PIC_TRACE(8);
+        compact_scan_body(c.s, st, c.cap, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
         PIC_TRACE(4);
         grid_barrier(st, seq, []() {});
         PIC_TRACE(5);
         compact_move_body(c.s, st, a.holes, a.movers);
         if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
+        if (threadIdx.x == 0) s_ticket = 0;
         PIC_TRACE(6);
         // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
         grid_barrier(st, seq, [&]() {
             step_end_body(st, c.cap, a.log, a.log_len, a.stop_at_zero);
             volatile DevState* v = st;
-            for (int k = 0; k < 3; ++k) { v->bbox_lo[cur][k] = kGrid; v->bbox_hi[cur][k] = -1; }
-            v->cur = cur ^ 1;
+            for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
+            v->cur = nxt;
             v->ticket = 0;
             v->n_unfinished = 0;
         });

@@ -4,7 +4,7 @@ import sys
 import numpy as np
 raw = open(sys.argv[1], "rb").read()
 steps, blocks = np.frombuffer(raw[:8], dtype=np.int32)
-t = np.frombuffer(raw[8:], dtype=np.uint64).reshape(steps, blocks, 8).astype(np.int64)
+t = np.frombuffer(raw[8:], dtype=np.uint64).reshape(steps, blocks, 16).astype(np.int64)
 names = ["own chunks of warp 0 (0->1)", "wait for block's other warps (1->2)", "barrier 1 (2->3)", "clear A + scan (3->4)",
          "barrier 2 (4->5)", "compact move (5->6)", "barrier 3 (6->7)"]
 good = t[:, 0, 7] > 0
@@ -13,5 +13,9 @@ print(f"{t.shape[0]} steps x {blocks} blocks; step time (first start -> last end
 for k, nm in enumerate(names):
     d = (t[:, :, k + 1] - t[:, :, k]) / 1e3
     print(f"  {nm:40s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
+for nm, a, b in (("clear A (3->8)", 3, 8), ("scan: counters + ts loads + masks (8->9)", 8, 9), ("scan: block reserve (9->10)", 9, 10), ("scan: list stores (10->4)", 10, 4)):
+    if t[:, :, a].min() > 0 and t[:, :, b].min() > 0:
+        d = (t[:, :, b] - t[:, :, a]) / 1e3
+        print(f"    {nm:40s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
 end_main = t[:, :, 2] - t[:, :, 0].min(1, keepdims=True)
 print(f"  block finishes main phase at: min {np.median(end_main.min(1))/1e3:.1f} median {np.median(end_main)/1e3:.1f} max {np.median(end_main.max(1))/1e3:.1f} us")
