@@ -12,10 +12,11 @@ the charge box is all-reduced over NCCL once per Poisson step.
   e2e       the same run driven through the C ABI with HOST buffers: the initial electrons are
             uploaded from pinned host memory and the final population is downloaded to pinned host
             memory inside the timed (wall-clock) region.
-  roofline  the scheduler kernel (k_mover): algorithmic bytes = 68 B per push
-            divided by its device time (CUDA events on the launching stream) vs measured HBM copy
-            bandwidth.  The kernel keeps an electron in registers for all 10 mobility steps, so the
-            68-B-accounted figure may exceed the HBM peak; DRAM traffic from ncu is under profiles/.
+  roofline  the dominant kernel (k_poisson_fused: one cooperative launch = the whole run of 100 Poisson
+            steps): algorithmic bytes = 68 B per push x pushes of the launch, divided by
+            its device time (CUDA events on the launching stream) vs measured HBM copy bandwidth.  The
+            kernel keeps an electron in registers for all 10 mobility steps, so the 68-B-accounted
+            figure may exceed the HBM peak; `traffic` is the DRAM traffic ncu measured for it.
   --impl reference   times the reference itself: its own CUDA program (oracle/_ref/main, built from
             the upstream sources where they lie) when it and a GPU are available, else the CPU port.
 """
@@ -245,7 +246,7 @@ def run_ours(args):
                 "what": "picb200_upload (pinned host SoA) + picb200_run_steps + picb200_download (pinned host SoA), wall clock"},
         "gpu_launches": int(prof["launches"]),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
-                     "kernel": "k_mover<persistent>", "launches": int(prof["mover_launches"]), "kernel_ms_total": prof["mover_ms"],
+                     "kernel": "k_poisson_fused", "launches": int(prof["mover_launches"]), "kernel_ms_total": prof["mover_ms"],
                      "kernel_share_of_step": prof["mover_ms"] / gpu_ms if gpu_ms else None,
                      "accounting": f"{BYTES_PER_PUSH:.0f} B per push x pushes per launch (SURVEY.md 8d); peak = {peak_src}; electrons stay in registers for all 10 mobility steps of a launch, so required HBM traffic is ~7.6 B/push and the 68-B-accounted figure may exceed the peak"},
         "phases_ms_per_step": {k: v for k, v in phases.items() if k.endswith("_ms")},
