@@ -148,8 +148,11 @@ def run_ours(args):
     eng = importlib.import_module("particle-simulation_b200")
     if eng.device_count() == 0:
         raise SystemExit("bench.py: no CUDA device; libpicb200 has no CPU fallback")
+    # N>1: the charge grid is exchanged inside the persistent kernel over NVLink peer memory (handles
+    # all-gathered over gloo below); PICB200_NCCL=1 selects the one-NCCL-all-reduce-per-Poisson-step path.
+    use_nccl = world > 1 and os.environ.get("PICB200_NCCL", "0") not in ("", "0")
     uid = None
-    if world > 1:
+    if use_nccl:
         obj = [eng.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(obj, src=0)
         uid = obj[0]
@@ -157,6 +160,11 @@ def run_ours(args):
     kw = dict(CFG2)
     kw["init_n"] = n_local * world
     sim = eng.Sim(device=local, rank=rank, nranks=world, nccl_unique_id=uid, **kw)
+    if world > 1 and not use_nccl:
+        handles = [None] * world
+        dist.all_gather_object(handles, sim.peer_export())
+        sim.peer_connect(handles)
+        dist.barrier()
     id_base = rank * n_local
     P = CFG2["poisson_steps"]
 
@@ -240,7 +248,7 @@ def run_ours(args):
         "ms_per_step": t_max * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "per_gpu_init_n": n_local, "global_init_n": n_local * world, "final_n_rank0": final["final_n"],
-                   "pushes_per_step_rank0": pushes // max(1, args.steps), "parallelism": f"particle slabs x{world}, charge-box allreduce per Poisson step" if world > 1 else "single GPU",
+                   "pushes_per_step_rank0": pushes // max(1, args.steps), "parallelism": (f"particle slabs x{world}, " + ("NCCL all-reduce of the charge box per Poisson step" if use_nccl else "charge box summed inside the persistent kernel over NVLink peer memory")) if world > 1 else "single GPU",
                    "l2": "flushed between runs (512 MiB memset); the 48 MB working set is L2-resident within a run, as it is for the reference"},
         "e2e": {"value": e2e_pushes_all / e2e_max, "unit": UNIT, "h2d_bytes_per_step": n_local * 48, "d2h_bytes_per_step": d2h_bytes // max(1, args.steps),
                 "what": "picb200_upload (pinned host SoA) + picb200_run_steps + picb200_download (pinned host SoA), wall clock"},

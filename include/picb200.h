@@ -55,7 +55,7 @@ typedef struct picb200_config {
      * one integer all-reduce of the charge box per Poisson step. */
     int32_t  rank;               /* 0-based */
     int32_t  nranks;             /* 1 = single GPU */
-    const void* nccl_unique_id;  /* 128-byte ncclUniqueId shared by all ranks; required when nranks > 1 */
+    const void* nccl_unique_id;  /* 128-byte ncclUniqueId shared by all ranks; NULL = no NCCL (use picb200_peer_connect) */
     int32_t  print_stdout;       /* 1 = print the reference's stdout lines (header, scheduler name, states, summary) */
     int32_t  reserved;
 } picb200_config;
@@ -164,6 +164,16 @@ int picb200_dev_philox(int32_t device, int64_t n, const uint32_t* ctr, const uin
 int picb200_dev_energy_index(int32_t device, int64_t n, const float* energy, int32_t* out);
 /* host-side loader (src/cross_section.cu:3-28): returns rows read, -1 if the file cannot be opened */
 int picb200_load_table(const char* path, float* rows2);
+
+/* ---- multi-GPU over NVLink peer memory (no reference counterpart: device 0 is hard-coded, src/pic.cu:394)
+ * With nranks > 1 the modes 30/33 kernel can exchange the charge grid itself, by reading the peers' local
+ * grids through NVLink, so that a whole run stays one launch per GPU.  Every rank exports a handle, the
+ * caller gathers the nranks handles in rank order (threads: shared array; processes: any all-gather) and
+ * every rank connects.  Works across threads of one process (peer access) and across processes (CUDA IPC).
+ * Without this call the engine falls back to one NCCL all-reduce per Poisson step (needs nccl_unique_id). */
+#define PICB200_PEER_HANDLE_BYTES 256
+int picb200_peer_export(picb200_sim* sim, void* handle_out /* PICB200_PEER_HANDLE_BYTES */);
+int picb200_peer_connect(picb200_sim* sim, const void* handles /* nranks x PICB200_PEER_HANDLE_BYTES */);
 
 /* NCCL bootstrap helper: writes a 128-byte ncclUniqueId (call on rank 0, broadcast it yourself) */
 int picb200_nccl_unique_id(void* out128);

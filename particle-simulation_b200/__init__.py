@@ -27,6 +27,7 @@ DEAD = -2
 TABLE_ROWS = 10000
 GRID = 512
 ABI_VERSION = 1
+PEER_HANDLE_BYTES = 256
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -110,6 +111,8 @@ SIGNATURES = {
     "picb200_dev_energy_index": (C.c_int, [C.c_int32, C.c_int64, _fp, _ip]),
     "picb200_load_table": (C.c_int, [C.c_char_p, _fp]),
     "picb200_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "picb200_peer_export": (C.c_int, [_sim, C.c_void_p]),
+    "picb200_peer_connect": (C.c_int, [_sim, C.c_void_p]),
 }
 for _name, (_res, _args) in SIGNATURES.items():
     _f = getattr(lib, _name)  # AttributeError here = the library does not export what the header declares
@@ -267,6 +270,19 @@ class Sim:
         _check(lib.picb200_download(self._h, C.byref(n), *[_ptr(getattr(st, k), _fp) for k in ("x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az")],
                                     _ptr(st.ts, _ip), _ptr(st.id, _up)))
         return n.value
+
+    def peer_export(self) -> bytes:
+        """This rank's 256-byte peer handle (include/picb200.h: picb200_peer_export)."""
+        b = C.create_string_buffer(PEER_HANDLE_BYTES)
+        _check(lib.picb200_peer_export(self._h, C.cast(b, C.c_void_p)))
+        return b.raw
+
+    def peer_connect(self, handles):
+        """handles: the handles of all ranks in rank order (list of bytes)."""
+        blob = b"".join(bytes(h) for h in handles)
+        assert len(blob) == PEER_HANDLE_BYTES * self.cfg.nranks
+        b = C.create_string_buffer(blob, len(blob))
+        _check(lib.picb200_peer_connect(self._h, C.cast(b, C.c_void_p)))
 
     def profile(self) -> dict:
         p = Profile()

@@ -19,6 +19,7 @@
 #include <limits>
 #include <string>
 #include <vector>
+#include <unistd.h>
 
 namespace picb200 {
 
@@ -93,7 +94,7 @@ struct Sim {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     Soa soa{};
     void* soa_base = nullptr;
-    int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
+    int* grid[kGrids] = {nullptr, nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
     int* holes = nullptr;
@@ -113,6 +114,15 @@ struct Sim {
     size_t box_buf_cells = 0;
     int* d_bbox_red = nullptr;
     int* h_bbox_red = nullptr;
+    // multi-GPU, peer mode: the exchange runs inside the fused kernel over NVLink peer mappings
+    PeerMailbox* mail = nullptr;         // written by the peers
+    PeerLocal* pl = nullptr;
+    PeerLocal* h_pl = nullptr;           // pinned mirror
+    PeerArgs pa{};
+    bool peer_connected = false;
+    std::vector<void*> ipc_opened;
+    int peer_export(void* out);
+    int peer_connect(const void* handles);
     // profiling: CUDA-event spans per phase on the launching stream + a count of kernel launches
     enum Phase { kPhDeposit = 0, kPhGather, kPhClear, kPhMover, kPhCompact, kPhCollective, kPhCount };
     struct Span { cudaEvent_t a, b; int phase; };
@@ -184,6 +194,11 @@ void Sim::release() {
     if (device >= 0 && (soa_base || st)) cudaSetDevice(device);
     if (comm && nccl) { nccl->commDestroy(comm); comm = nullptr; }
     if (stream) { cudaStreamSynchronize(stream); }
+    for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
+    ipc_opened.clear();
+    cudaFree(mail); mail = nullptr;
+    cudaFree(pl); pl = nullptr;
+    if (h_pl) { cudaFreeHost(h_pl); h_pl = nullptr; }
     cudaFree(soa_base); soa_base = nullptr;
     for (int g = 0; g < kGrids; ++g) { cudaFree(grid[g]); grid[g] = nullptr; }
     cudaFree(holes); holes = nullptr;
@@ -264,7 +279,7 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&movers, list_cap * 4), "Minor alloc");
 
     // ---- charge grid 512^3 int32, zeroed once (src/pic.cu:448-450 allocates 2 GiB of 16-B cells)
-    for (int g = 0; g < kGrids; ++g) {
+    for (int g = 0; g < (cfg.nranks > 1 ? kGrids : kRot); ++g) {
         CK(cudaMalloc(&grid[g], (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
         CK(cudaMemsetAsync(grid[g], 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
     }
@@ -279,37 +294,112 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMemsetAsync(log, 0, sizeof(StepLog) * (size_t)log_len, stream), "Minor alloc");
 
     CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
     fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
     if (cfg.nranks > 1) {
-        nccl = load_nccl(g_last_error);
-        if (!nccl) return 1;
-        if (!cfg.nccl_unique_id) return fail("nranks > 1 needs nccl_unique_id", "NCCL init");
-        NcclUniqueId id;
-        memcpy(&id, cfg.nccl_unique_id, sizeof(id));
-        int r = nccl->commInitRank(&comm, cfg.nranks, id, cfg.rank);
-        if (r != 0) return fail(std::string("ncclCommInitRank: ") + nccl->getErrorString(r), "NCCL init");
-        CK(cudaMalloc(&d_bbox_red, 8 * sizeof(int)), "Minor alloc");
-        CK(cudaMallocHost(&h_bbox_red, 8 * sizeof(int)), "Minor alloc");
+        if (cfg.nranks > kMaxRanks) return fail("at most 8 ranks", "picb200_create");
+        CK(cudaMalloc(&mail, sizeof(PeerMailbox)), "Minor alloc");
+        CK(cudaMemsetAsync(mail, 0, sizeof(PeerMailbox), stream), "Minor alloc");
+        CK(cudaMalloc(&pl, sizeof(PeerLocal)), "Minor alloc");
+        CK(cudaMemsetAsync(pl, 0, sizeof(PeerLocal), stream), "Minor alloc");
+        CK(cudaMallocHost(&h_pl, sizeof(PeerLocal)), "Minor alloc");
+        memset(h_pl, 0, sizeof(PeerLocal));
+        if (cfg.nccl_unique_id) {            // NCCL path (baseline / no peer access): one communicator per rank
+            nccl = load_nccl(g_last_error);
+            if (!nccl) return 1;
+            NcclUniqueId id;
+            memcpy(&id, cfg.nccl_unique_id, sizeof(id));
+            int r = nccl->commInitRank(&comm, cfg.nranks, id, cfg.rank);
+            if (r != 0) return fail(std::string("ncclCommInitRank: ") + nccl->getErrorString(r), "NCCL init");
+            CK(cudaMalloc(&d_bbox_red, 8 * sizeof(int)), "Minor alloc");
+            CK(cudaMallocHost(&h_bbox_red, 8 * sizeof(int)), "Minor alloc");
+        }
     }
     CK(cudaStreamSynchronize(stream), "Setup");
     CK_LAST("Setup");
     return 0;
 }
 
+// What one rank tells the others (picb200_peer_export -> picb200_peer_connect): where its two local
+// deposit grids and its mailbox live.  Same process (one host thread per GPU): raw pointers + peer access.
+// Other process (one process per GPU, e.g. torchrun): CUDA IPC handles.
+struct PeerHandle {
+    unsigned magic;
+    int device;
+    long long pid;
+    void* raw[3];                    // local grid 0, local grid 1, mailbox
+    cudaIpcMemHandle_t ipc[3];
+};
+static_assert(sizeof(PeerHandle) <= PICB200_PEER_HANDLE_BYTES, "handle fits the ABI blob");
+
+int Sim::peer_export(void* out) {
+    if (cfg.nranks < 2 || !mail) return fail("peer export needs nranks > 1", "Peer setup");
+    CK(cudaSetDevice(device), "Set device");
+    PeerHandle h;
+    memset(&h, 0, sizeof(h));
+    h.magic = 0x50494342u;
+    h.device = device;
+    h.pid = (long long)getpid();
+    h.raw[0] = grid[0]; h.raw[1] = grid[1]; h.raw[2] = mail;
+    for (int k = 0; k < 3; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
+    memset(out, 0, PICB200_PEER_HANDLE_BYTES);
+    memcpy(out, &h, sizeof(h));
+    return 0;
+}
+
+int Sim::peer_connect(const void* handles) {
+    if (cfg.nranks < 2 || !mail) return fail("peer connect needs nranks > 1", "Peer setup");
+    CK(cudaSetDevice(device), "Set device");
+    memset(&pa, 0, sizeof(pa));
+    pa.rank = cfg.rank;
+    pa.nranks = cfg.nranks;
+    pa.pl = pl;
+    for (int r = 0; r < cfg.nranks; ++r) {
+        PeerHandle h;
+        memcpy(&h, static_cast<const unsigned char*>(handles) + (size_t)r * PICB200_PEER_HANDLE_BYTES, sizeof(h));
+        if (h.magic != 0x50494342u) return fail("bad peer handle", "Peer setup");
+        void* p[3] = {nullptr, nullptr, nullptr};
+        if (r == cfg.rank) {
+            p[0] = grid[0]; p[1] = grid[1]; p[2] = mail;
+        } else if (h.pid == (long long)getpid()) {
+            int can = 0;
+            CK(cudaDeviceCanAccessPeer(&can, device, h.device), "Peer setup");
+            if (!can) return fail("GPUs cannot access each other's memory", "Peer setup");
+            cudaError_t e = cudaDeviceEnablePeerAccess(h.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(cudaGetErrorString(e), "Peer setup (enable peer access)");
+            cudaGetLastError();
+            for (int k = 0; k < 3; ++k) p[k] = h.raw[k];
+        } else {
+            for (int k = 0; k < 3; ++k) {
+                CK(cudaIpcOpenMemHandle(&p[k], h.ipc[k], cudaIpcMemLazyEnablePeerAccess), "Peer setup (cudaIpcOpenMemHandle)");
+                ipc_opened.push_back(p[k]);
+            }
+        }
+        pa.loc[r][0] = static_cast<const int*>(p[0]);
+        pa.loc[r][1] = static_cast<const int*>(p[1]);
+        pa.mail[r] = static_cast<PeerMailbox*>(p[2]);
+    }
+    peer_connected = true;
+    return 0;
+}
+
 int Sim::sync_state() {
     CK(cudaMemcpyAsync(h_st, st, sizeof(DevState), cudaMemcpyDeviceToHost, stream), "State readback");
+    if (pl) CK(cudaMemcpyAsync(h_pl, pl, sizeof(PeerLocal), cudaMemcpyDeviceToHost, stream), "State readback");
     CK(cudaStreamSynchronize(stream), "State readback");
     cur = h_st->cur;
+    if (pl && h_pl->error) return fail("a peer rank did not reach the charge exchange within 20 s", "Charge exchange");
     return collect_spans();
 }
 
 // A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
 int Sim::reset_state() {
     // a deposit of the previous population may still sit in either grid: both boxes bound it
-    for (int g = 0; g < kGrids; ++g) k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[g], g);
+    for (int g = 0; g < kGrids; ++g)
+        if (grid[g]) k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[g], g);
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
     k_reset_bbox<<<1, 32, 0, stream>>>(st, kGrids);
     CK_LAST("Reset state");
@@ -367,6 +457,7 @@ int Sim::op_clear() {
 // {-lo, hi}), pack it contiguously, one integer ncclAllReduce over NVLink, unpack.
 // Integer sums are order-independent, so every rank holds bit-identical counts.
 int Sim::allreduce_charge() {
+    if (!comm) return fail("this multi-GPU phase needs the NCCL path: pass nccl_unique_id at creation", "Charge all-reduce");
     k_bbox_encode<<<1, 32, 0, stream>>>(st, d_bbox_red, cur);
     launches += 4;   // encode, decode, pack, unpack (NCCL's own kernels are not counted)
     int r = nccl->allReduce(d_bbox_red, d_bbox_red, 8, kNcclInt32, kNcclMax, comm, stream);
@@ -471,14 +562,18 @@ int Sim::op_step_end() {
 // Modes 30/33: `steps` iterations of runPIC's loop (src/pic.cu:487-560) in one cooperative launch.
 // Several ranks: one step per launch, with the charge all-reduce in between.
 int Sim::fused_steps(int steps) {
-    if (!charge_valid) {                    // first step after init/upload: grid[cur] needs this population's deposit
+    const bool peer = cfg.nranks > 1 && peer_connected;      // exchange inside the kernel, whole run in one launch
+    if (cfg.nranks > 1 && !peer && !comm)
+        return fail("several ranks need picb200_peer_connect() or an nccl_unique_id", "Mobility steps");
+    if (!charge_valid && !peer) {           // first step after init/upload: grid[cur] needs this population's deposit
         if (op_clear() || op_deposit()) return 1;
     }
-    const int per_launch = cfg.nranks > 1 ? 1 : steps;
+    const int per_launch = (cfg.nranks > 1 && !peer) ? 1 : steps;
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
-        FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
-                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr};
+        FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2], grid[3]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0};
+        charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
         const size_t trace_words = (size_t)per_launch * (size_t)sm_count * 16;
@@ -488,8 +583,8 @@ int Sim::fused_steps(int steps) {
         }
         void* args[] = {&a};
         span_begin(kPhMover);
-        CK(cudaLaunchCooperativeKernel((const void*)k_poisson_fused, dim3((unsigned)sm_count), dim3((unsigned)mover_threads), args,
-                                       (size_t)kFusedSmemBytes(mover_threads), stream),
+        CK(cudaLaunchCooperativeKernel(peer ? (const void*)k_poisson_fused<true> : (const void*)k_poisson_fused<false>, dim3((unsigned)sm_count),
+                                       dim3((unsigned)mover_threads), args, (size_t)kFusedSmemBytes(mover_threads), stream),
            "Mobility steps");
         ++launches; ++mover_launches;
         span_end();
@@ -498,15 +593,16 @@ int Sim::fused_steps(int steps) {
             CK(cudaMemcpyAsync(h.data(), a.trace, trace_words * 8, cudaMemcpyDeviceToHost, stream), "Trace readback");
             CK(cudaStreamSynchronize(stream), "Trace readback");
             cudaFree(a.trace);
-            if (FILE* f = fopen(trace_path, "wb")) {
+            const std::string tp = cfg.nranks > 1 ? std::string(trace_path) + "." + std::to_string(cfg.rank) : std::string(trace_path);
+            if (FILE* f = fopen(tp.c_str(), "wb")) {
                 const int hdr[2] = {per_launch, sm_count};
                 fwrite(hdr, sizeof(int), 2, f);
                 fwrite(h.data(), 8, trace_words, f);
                 fclose(f);
             }
         }
-        if (cfg.nranks > 1) {               // the kernel deposited this rank's survivors into the other grid
-            cur = (cur + 1) % kGrids;
+        if (cfg.nranks > 1 && !peer) {      // NCCL path: the kernel deposited this rank's survivors into the next grid
+            cur = (cur + 1) % kRot;
             span_begin(kPhCollective);
             const int rc = allreduce_charge();
             span_end();
@@ -718,7 +814,7 @@ int picb200_get_profile(picb200_sim* sim, picb200_profile* out) {
 int picb200_flush_l2(picb200_sim* sim) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
-    CK(cudaMemsetAsync(s.grid[(s.cur + 1) % kGrids], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
+    CK(cudaMemsetAsync(s.grid[(s.cur + 1) % (s.cfg.nranks > 1 ? kGrids : kRot)], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
     CK(cudaStreamSynchronize(s.stream), "Flush L2");
     return 0;
 }
@@ -823,6 +919,9 @@ int picb200_load_table(const char* path, float* rows2) {
 }
 // host-side copy of the edge table, for the exhaustive CPU check of the device formula
 void picb200_host_energy_edges(float* out_edges) { build_energy_edges(out_edges); }
+
+int picb200_peer_export(picb200_sim* sim, void* handle_out) { return sim->s.peer_export(handle_out); }
+int picb200_peer_connect(picb200_sim* sim, const void* handles) { return sim->s.peer_connect(handles); }
 
 int picb200_nccl_unique_id(void* out128) {
     NcclApi* api = load_nccl(g_last_error);

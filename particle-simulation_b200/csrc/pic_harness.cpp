@@ -3,7 +3,10 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <condition_variable>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <tuple>
@@ -24,11 +27,25 @@ int picb200_harness_run(const picb200_config* cfg_in, int gpus) {
         printf("CUDA error: %d GPUs requested, %d visible\nAt: Setup\n", gpus, picb200_device_count());
         return 1;
     }
+    // One host thread and one picb200 rank per GPU.  The ranks exchange peer handles (threads of one
+    // process: a shared array and a barrier) so that the charge grid is summed inside the persistent
+    // kernel over NVLink; PICB200_NCCL=1 selects the NCCL all-reduce path instead.
+    const bool use_nccl = getenv("PICB200_NCCL") && atoi(getenv("PICB200_NCCL")) != 0;
     char uid[128];
-    if (picb200_nccl_unique_id(uid)) return 1;
+    if (use_nccl && picb200_nccl_unique_id(uid)) return 1;
     std::vector<picb200_summary> sums((size_t)gpus);
     std::vector<int> rcs((size_t)gpus, 0);
     std::vector<std::string> errs((size_t)gpus);
+    std::vector<unsigned char> handles((size_t)gpus * PICB200_PEER_HANDLE_BYTES, 0);
+    std::mutex mu;
+    std::condition_variable cv;
+    int arrived = 0, generation = 0;
+    auto barrier = [&]() {
+        std::unique_lock<std::mutex> lk(mu);
+        const int gen = generation;
+        if (++arrived == gpus) { arrived = 0; ++generation; cv.notify_all(); }
+        else cv.wait(lk, [&] { return generation != gen; });
+    };
     std::vector<std::thread> th;
     for (int r = 0; r < gpus; ++r) {
         th.emplace_back([&, r]() {
@@ -37,10 +54,38 @@ int picb200_harness_run(const picb200_config* cfg_in, int gpus) {
             c.nranks = gpus;
             c.device = r;
             c.capacity = base.capacity / gpus;
-            c.nccl_unique_id = uid;
+            c.nccl_unique_id = use_nccl ? uid : nullptr;
             c.print_stdout = 0;
-            rcs[(size_t)r] = picb200_run(&c, &sums[(size_t)r], nullptr, 0);
-            if (rcs[(size_t)r]) errs[(size_t)r] = picb200_last_error();
+            int& rc = rcs[(size_t)r];
+            if (use_nccl) {
+                rc = picb200_run(&c, &sums[(size_t)r], nullptr, 0);
+                if (rc) errs[(size_t)r] = picb200_last_error();
+                return;
+            }
+            picb200_sim* sim = nullptr;
+            rc = picb200_create(&c, &sim);
+            if (!rc) rc = picb200_peer_export(sim, handles.data() + (size_t)r * PICB200_PEER_HANDLE_BYTES);
+            if (rc) errs[(size_t)r] = picb200_last_error();
+            barrier();                                  // every handle is in place (or a rank failed)
+            bool all_ok = true;
+            for (int q = 0; q < gpus; ++q) all_ok = all_ok && rcs[(size_t)q] == 0;
+            if (all_ok) {
+                rc = picb200_peer_connect(sim, handles.data());
+                // particle slab of this rank: ids [r*n/k, (r+1)*n/k)
+                const long long lo = (long long)base.init_n * r / gpus, hi = (long long)base.init_n * (r + 1) / gpus;
+                if (!rc) rc = picb200_init_uniform(sim, (int32_t)(hi - lo), (uint64_t)lo);
+                if (rc) errs[(size_t)r] = picb200_last_error();
+            }
+            barrier();                                  // nobody launches unless everybody connected
+            all_ok = true;
+            for (int q = 0; q < gpus; ++q) all_ok = all_ok && rcs[(size_t)q] == 0;
+            if (all_ok) {
+                rc = picb200_run_steps(sim, base.poisson_steps);
+                if (!rc) rc = picb200_get_summary(sim, &sums[(size_t)r]);
+                if (rc) errs[(size_t)r] = picb200_last_error();
+            }
+            barrier();                                  // no rank frees a grid a peer may still map
+            if (sim) picb200_destroy(sim);
         });
     }
     for (auto& t : th) t.join();

@@ -331,6 +331,8 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
 // The reference needs 6 kernels, 3 memsets, 1 H2D and 2 blocking D2H copies for the same work
 // (src/pic.cu:495-553); here the host enqueues one kernel for any number of Poisson steps.
 // =============================================================================================
+#include "pic_peer.cuh"
+
 struct FusedArgs {
     Soa s;
     DevState* st;
@@ -344,6 +346,8 @@ struct FusedArgs {
     double efc;
     uint2 seed;
     unsigned long long* trace;   // optional (PICB200_TRACE): 16 globaltimer stamps per block per Poisson step
+    PeerArgs peer;               // kPeer only
+    int initial_deposit;         // kPeer only: no summed grid holds this population yet
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -594,6 +598,7 @@ constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
 constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * kStageBytesPerWarp; }
 
+template <bool kPeer>
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_box[6];
@@ -627,13 +632,54 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     f.efc = a.efc;
 
     unsigned seq = 0;
+    const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
+    unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
+    if (kPeer) {
+        xe = ld_sys_u32(&a.peer.pl->xseq);
+        if (a.initial_deposit) {
+            // particlesToGrid of the first Poisson step for a fresh population: local deposit, exchange, sum
+            const unsigned e = xe + 1u;
+            const int lg = (int)(e & 1u);
+            const int n = min(ld_volatile_i32(&st->n), a.capacity);
+            const int rounded = (n + 31) & ~31;
+            for (int i = (gwarp << 5) + c.lane; i < rounded; i += nwarp << 5) {
+                const bool in = i < n;
+                const float px = in ? __ldcg(c.s.x + i) : 0.f, py = in ? __ldcg(c.s.y + i) : 0.f, pz = in ? __ldcg(c.s.z + i) : 0.f;
+                deposit_lanes(a.grid[lg], in, cell_of_fast(px, f.bnd), cell_of_fast(py, f.bnd), cell_of_fast(pz, f.bnd), c.lane, s_box);
+            }
+            __syncthreads();
+            if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
+                atomicMin(&st->bbox_lo[lg][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[lg][threadIdx.x], s_box[3 + threadIdx.x]);
+            }
+            grid_barrier(st, seq, [&]() { peer_exchange_boxes(st, a.peer, lg, e); });
+            {
+                PeerPull pp;
+                peer_pull_issue(st, a.peer, lg, 2 + lg, gwarp, c.lane, pp);
+                peer_pull_finish(a.peer, lg, a.grid[2 + lg], gwarp, nwarp, c.lane, pp);
+            }
+            if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
+            grid_barrier(st, seq, [&]() {
+                volatile DevState* v = st;
+                for (int k = 0; k < 3; ++k) { v->bbox_lo[2 + lg][k] = v->xbox_lo[k]; v->bbox_hi[2 + lg][k] = v->xbox_hi[k]; }
+                v->cur = 2 + lg;
+                st_sys_u32(&a.peer.pl->xseq, e);
+                if (a.steps == 0) peer_finish(a.peer, e);
+            });
+            xe = e;
+        }
+    }
     for (int step = 0; step < a.steps; ++step) {
         if (ld_volatile_i32(&st->hit_zero)) break;          // uniform: set before the previous barrier 3 released
         const int cur = ld_volatile_i32(&st->cur);
-        const int nxt = (cur + 1) % kGrids, old = (cur + 2) % kGrids;
+        // single GPU: three grids in rotation.  Peer mode: gather from the summed grid of exchange xe,
+        // deposit into local grid (xe+1)&1, whose sum over the ranks lands in grid 2+((xe+1)&1).
+        const int nxt = kPeer ? (int)((xe + 1u) & 1u) : (cur + 1) % kRot;
+        const int old = kPeer ? (int)(xe & 1u) : (cur + 2) % kRot;
         f.A = a.grid[cur];       // gathered from
-        f.B = a.grid[nxt];       // receives the deposit of the next Poisson step
-                                 // a.grid[old] was gathered from one step ago and is emptied below
+        f.B = a.grid[nxt];       // receives the (local) deposit of the next Poisson step
+                                 // a.grid[old]: single GPU: gathered from one step ago, emptied below;
+                                 // peer mode: the local deposit of the previous exchange, emptied after the next
         c.g0 = (unsigned)ld_volatile_i32(&st->poisson_index) * (unsigned)a.pt;
         const int n0 = min(ld_volatile_i32(&st->n), c.cap);
         const int chunks = (n0 + 31) >> 5;
@@ -657,7 +703,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         while (staged) fused_staged(c, f, staged, pushes, dead);
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
-        clear_box_rows(st, a.grid[old], old, (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), (int)(gridDim.x * (blockDim.x >> 5)), c.lane);
+        if (!kPeer) clear_box_rows(st, a.grid[old], old, gwarp, nwarp, c.lane);
         PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
         // ---- barrier 1 (+ fall-back passes over spilled children)
@@ -687,6 +733,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 const int unfinished = ld_volatile_i32(&st->n_unfinished);
                 st->n_unfinished = 0;
                 st->gen_hi = unfinished > 0 ? min(ld_volatile_i32(&st->n_alloc), c.cap) : -1;
+                // every local deposit of this step is in place: meet the other ranks
+                if (kPeer && unfinished <= 0) peer_exchange_boxes(st, a.peer, nxt, xe + 1u);
             });
             const int hi = ld_volatile_i32(&st->gen_hi);
             if (hi < 0) break;
@@ -701,8 +749,19 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
 
         // ---- every push of this step is done: list the holes and movers
         PIC_TRACE(3);          // barrier 1 passed
+        PeerPull pp;
+        if (kPeer) {
+            // sum of all ranks' local grids -> the grid the next step gathers from: the loads over NVLink
+            // start here and are consumed after the compaction scan.  Nobody pulls from the previous
+            // local grid any more (every rank has passed the exchange above), so empty it.
+            peer_pull_issue(st, a.peer, nxt, 2 + nxt, gwarp, c.lane, pp);
+            PIC_TRACE(11);
+            clear_box_rows(st, a.grid[old], old, gwarp, nwarp, c.lane);
+        }
         PIC_TRACE(8);
         compact_scan_body(c.s, st, c.cap, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
+        if (kPeer) peer_pull_finish(a.peer, nxt, a.grid[2 + nxt], gwarp, nwarp, c.lane, pp);
+        PIC_TRACE(12);
         PIC_TRACE(4);
         grid_barrier(st, seq, []() {});
         PIC_TRACE(5);
@@ -715,10 +774,18 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             step_end_body(st, c.cap, a.log, a.log_len, a.stop_at_zero);
             volatile DevState* v = st;
             for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
-            v->cur = nxt;
+            if (kPeer) {
+                for (int k = 0; k < 3; ++k) { v->bbox_lo[2 + nxt][k] = v->xbox_lo[k]; v->bbox_hi[2 + nxt][k] = v->xbox_hi[k]; }
+                v->cur = 2 + nxt;
+                st_sys_u32(&a.peer.pl->xseq, xe + 1u);
+                if (step == a.steps - 1) peer_finish(a.peer, xe + 1u);
+            } else {
+                v->cur = nxt;
+            }
             v->ticket = 0;
             v->n_unfinished = 0;
         });
+        ++xe;
         PIC_TRACE(7);
     }
 }

@@ -1,0 +1,116 @@
+"""Multi-GPU parity (needs >= 2 B200s: `gpurun --gpus 2 -- python -m pytest tests/test_multi_gpu.py -m gpu`).
+
+Particle slabs: rank r owns initial ids [r*n/k, (r+1)*n/k); the only coupling is the charge grid, summed
+over the ranks once per Poisson step -- inside the persistent kernel over NVLink peer memory
+(picb200_peer_connect), or by one NCCL all-reduce per step (nccl_unique_id).  Philox is keyed on the
+particle id, so the union of the slabs must equal the single-population oracle run bit for bit.
+"""
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+F32 = ("x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az")
+
+
+def run_ranks(engine, k, transport, mode, n, cap, pt, steps_list, pos=None, vel=None, launches_per_entry=1):
+    """Run k ranks in k host threads of this process; returns per-rank (summary, State) after each entry of steps_list."""
+    uid = engine.nccl_unique_id() if transport == "nccl" else None
+    handles = [None] * k
+    out = [[] for _ in range(k)]
+    err = []
+    bar = threading.Barrier(k)
+
+    def work(r):
+        try:
+            sim = engine.Sim(mode=mode, capacity=cap // k, poisson_timestep=pt, poisson_steps=sum(steps_list), device=r, rank=r, nranks=k, nccl_unique_id=uid)
+            if transport == "peer":
+                handles[r] = sim.peer_export()
+                bar.wait()
+                sim.peer_connect(handles)
+            lo, hi = n * r // k, n * (r + 1) // k
+            if pos is None:
+                sim.init_uniform(hi - lo, lo)
+            else:
+                sim.upload(*[a[lo:hi] for a in pos], *[a[lo:hi] for a in vel], id=np.arange(lo, hi, dtype=np.uint64))
+            bar.wait()
+            for st in steps_list:
+                sim.run_steps(st)
+                out[r].append((sim.summary(), sim.download()))
+            bar.wait()
+            sim.close()
+        except Exception as e:  # noqa: BLE001
+            err.append((r, repr(e)))
+            bar.abort()
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(k)]
+    [t.start() for t in th]
+    [t.join(timeout=300) for t in th]
+    assert not err, err
+    return out
+
+
+def union_sorted(states):
+    ids = np.concatenate([s.id for s in states])
+    o = np.argsort(ids, kind="stable")
+    return {f: np.concatenate([getattr(s, f) for s in states])[o] for f in F32 + ("ts", "id")}
+
+
+def need_gpus(engine, k):
+    if engine.device_count() < k:
+        pytest.skip(f"needs {k} CUDA devices, {engine.device_count()} visible")
+
+
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
+@pytest.mark.parametrize("k", [2])
+def test_slabs_equal_single_population_oracle(engine, oracle, transport, k):
+    need_gpus(engine, k)
+    n, pt, cap = 40000, 10, 400000
+    rng = np.random.default_rng(3)
+    pos = rng.uniform(2.45, 2.65, size=(3, n)).astype(np.float32)     # dense: ~5 electrons per cell, real fields
+    vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)          # hot: collisions from the first push
+    steps_list = [1, 3, 2]                                             # several launches: the exchange state carries over
+    res = run_ranks(engine, k, transport, 0, n, cap, pt, steps_list, pos, vel)
+    o = oracle.Oracle(capacity=cap, poisson_timestep=pt, threads=4)
+    o.upload(*pos, *vel)
+    for j, st in enumerate(steps_list):
+        o.run(st)
+        c, ref = o.counters(), o.download_sorted()
+        sums = [res[r][j][0] for r in range(k)]
+        assert sum(s["final_n"] for s in sums) == c["n"]
+        assert sum(s["total_added"] for s in sums) == c["added"] and sum(s["total_removed"] for s in sums) == c["removed"]
+        assert sum(s["pushes"] for s in sums) == c["pushes"]
+        u = union_sorted([res[r][j][1] for r in range(k)])
+        assert np.array_equal(u["id"], ref["id"]) and np.array_equal(u["ts"], ref["ts"])
+        for f in F32:
+            assert np.array_equal(u[f], ref[f].astype(np.float32)), (transport, j, f)
+    assert c["added"] > 1000 and c["removed"] > 1000
+
+
+@pytest.mark.parametrize("k", [2, 4, 8])
+def test_peer_mode_equals_single_gpu_run(engine, k):
+    """cfg1-shaped run (collision free) and a short colliding run: k slabs == 1 GPU, after sorting by id."""
+    need_gpus(engine, k)
+    n, pt, cap, P = 64000, 10, 1024000, 12
+    with engine.Sim(mode=0, capacity=cap, poisson_timestep=pt, poisson_steps=P) as one:
+        one.init_uniform(n)
+        one.run_steps(P)
+        s1, d1 = one.summary(), one.download().sorted_by_id()
+    res = run_ranks(engine, k, "peer", 0, n, cap, pt, [P])
+    sums = [res[r][0][0] for r in range(k)]
+    assert sum(s["final_n"] for s in sums) == s1["final_n"] and sum(s["pushes"] for s in sums) == s1["pushes"]
+    u = union_sorted([res[r][0][1] for r in range(k)])
+    assert np.array_equal(u["id"], d1.id)
+    for f in F32:
+        assert np.array_equal(u[f], getattr(d1, f)), f
+
+
+def test_empty_rank_keeps_stepping(engine):
+    """A rank whose slab is empty still takes part in every exchange (no deadlock, right field)."""
+    need_gpus(engine, 2)
+    n, pt, cap = 1, 5, 1000       # rank 0 gets 0 electrons, rank 1 gets 1
+    res = run_ranks(engine, 2, "peer", 0, n, cap, pt, [3])
+    assert res[0][0][0]["final_n"] + res[1][0][0]["final_n"] == 1
+    assert res[0][0][0]["pushes"] + res[1][0][0]["pushes"] == 15
