@@ -17,8 +17,7 @@ namespace picb200 {
 constexpr int kGrid = 512;              // src/cell.cu:3
 constexpr int kRows = 10000;            // src/cross_section.h:9
 constexpr int kDead = -2;               // src/electron.h:8
-constexpr int kGrids = 4;               // charge grids: single GPU rotates 0..2 (gather / next deposit / being emptied);
-                                        // multi-GPU peer mode: 0,1 = local deposits (read by the peers), 2,3 = their sums
+constexpr int kGrids = 3;               // charge grids in rotation (gather / next deposit / being emptied)
 constexpr int kRot = 3;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr uint32_t kTagCollide = 0u, kTagInit = 1u;
@@ -45,7 +44,6 @@ struct DevState {
     int gen_hi;             // end of the fall-back window agreed at the barrier (-1: none)
     int n_unfinished;       // children spilled to the global store before they were pushed to the end
     int bbox_lo[kGrids][3], bbox_hi[kGrids][3];  // cell bounding box of the counts deposited in each charge grid
-    int xbox_lo[3], xbox_hi[3];  // multi-GPU: union over the ranks of the boxes of the exchange in flight
     int cur;                // which of the charge grids holds the current deposit
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)

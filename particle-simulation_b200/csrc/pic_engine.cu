@@ -94,7 +94,7 @@ struct Sim {
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     Soa soa{};
     void* soa_base = nullptr;
-    int* grid[kGrids] = {nullptr, nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
+    int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
     int* holes = nullptr;
@@ -116,6 +116,8 @@ struct Sim {
     int* h_bbox_red = nullptr;
     // multi-GPU, peer mode: the exchange runs inside the fused kernel over NVLink peer mappings
     PeerMailbox* mail = nullptr;         // written by the peers
+    int* recv = nullptr;                 // 2 parities x nranks grids: slot [p][rank] = own deposit, the others are written by the peers
+    int* own_peer_grid(int p) const { return recv + ((size_t)(p * cfg.nranks + cfg.rank) << kCellsLog2); }
     PeerLocal* pl = nullptr;
     PeerLocal* h_pl = nullptr;           // pinned mirror
     PeerArgs pa{};
@@ -197,6 +199,7 @@ void Sim::release() {
     for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
     ipc_opened.clear();
     cudaFree(mail); mail = nullptr;
+    cudaFree(recv); recv = nullptr;
     cudaFree(pl); pl = nullptr;
     if (h_pl) { cudaFreeHost(h_pl); h_pl = nullptr; }
     cudaFree(soa_base); soa_base = nullptr;
@@ -279,7 +282,7 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&movers, list_cap * 4), "Minor alloc");
 
     // ---- charge grid 512^3 int32, zeroed once (src/pic.cu:448-450 allocates 2 GiB of 16-B cells)
-    for (int g = 0; g < (cfg.nranks > 1 ? kGrids : kRot); ++g) {
+    for (int g = 0; g < kGrids; ++g) {
         CK(cudaMalloc(&grid[g], (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
         CK(cudaMemsetAsync(grid[g], 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
     }
@@ -330,28 +333,34 @@ struct PeerHandle {
     unsigned magic;
     int device;
     long long pid;
-    void* raw[3];                    // local grid 0, local grid 1, mailbox
-    cudaIpcMemHandle_t ipc[3];
+    void* raw[2];                    // block of 2 x nranks grids, mailbox
+    cudaIpcMemHandle_t ipc[2];
 };
 static_assert(sizeof(PeerHandle) <= PICB200_PEER_HANDLE_BYTES, "handle fits the ABI blob");
 
 int Sim::peer_export(void* out) {
     if (cfg.nranks < 2 || !mail) return fail("peer export needs nranks > 1", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
+    if (!recv) {     // one grid per (parity, rank): 2 x nranks x 512 MiB, zeroed once, then kept zero outside the boxes
+        const size_t bytes = ((size_t)2 * (size_t)cfg.nranks << kCellsLog2) * sizeof(int);
+        CK(cudaMalloc(&recv, bytes), "Peer grid alloc");
+        CK(cudaMemsetAsync(recv, 0, bytes, stream), "Peer grid alloc");
+        CK(cudaStreamSynchronize(stream), "Peer grid alloc");
+    }
     PeerHandle h;
     memset(&h, 0, sizeof(h));
     h.magic = 0x50494342u;
     h.device = device;
     h.pid = (long long)getpid();
-    h.raw[0] = grid[0]; h.raw[1] = grid[1]; h.raw[2] = mail;
-    for (int k = 0; k < 3; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
+    h.raw[0] = recv; h.raw[1] = mail;
+    for (int k = 0; k < 2; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
     memset(out, 0, PICB200_PEER_HANDLE_BYTES);
     memcpy(out, &h, sizeof(h));
     return 0;
 }
 
 int Sim::peer_connect(const void* handles) {
-    if (cfg.nranks < 2 || !mail) return fail("peer connect needs nranks > 1", "Peer setup");
+    if (cfg.nranks < 2 || !mail || !recv) return fail("peer connect needs nranks > 1 and a prior picb200_peer_export", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
     memset(&pa, 0, sizeof(pa));
     pa.rank = cfg.rank;
@@ -361,9 +370,9 @@ int Sim::peer_connect(const void* handles) {
         PeerHandle h;
         memcpy(&h, static_cast<const unsigned char*>(handles) + (size_t)r * PICB200_PEER_HANDLE_BYTES, sizeof(h));
         if (h.magic != 0x50494342u) return fail("bad peer handle", "Peer setup");
-        void* p[3] = {nullptr, nullptr, nullptr};
+        void* p[2] = {nullptr, nullptr};
         if (r == cfg.rank) {
-            p[0] = grid[0]; p[1] = grid[1]; p[2] = mail;
+            p[0] = recv; p[1] = mail;
         } else if (h.pid == (long long)getpid()) {
             int can = 0;
             CK(cudaDeviceCanAccessPeer(&can, device, h.device), "Peer setup");
@@ -371,16 +380,15 @@ int Sim::peer_connect(const void* handles) {
             cudaError_t e = cudaDeviceEnablePeerAccess(h.device, 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(cudaGetErrorString(e), "Peer setup (enable peer access)");
             cudaGetLastError();
-            for (int k = 0; k < 3; ++k) p[k] = h.raw[k];
+            for (int k = 0; k < 2; ++k) p[k] = h.raw[k];
         } else {
-            for (int k = 0; k < 3; ++k) {
+            for (int k = 0; k < 2; ++k) {
                 CK(cudaIpcOpenMemHandle(&p[k], h.ipc[k], cudaIpcMemLazyEnablePeerAccess), "Peer setup (cudaIpcOpenMemHandle)");
                 ipc_opened.push_back(p[k]);
             }
         }
-        pa.loc[r][0] = static_cast<const int*>(p[0]);
-        pa.loc[r][1] = static_cast<const int*>(p[1]);
-        pa.mail[r] = static_cast<PeerMailbox*>(p[2]);
+        pa.recv[r] = static_cast<int*>(p[0]);
+        pa.mail[r] = static_cast<PeerMailbox*>(p[1]);
     }
     peer_connected = true;
     return 0;
@@ -398,8 +406,8 @@ int Sim::sync_state() {
 // A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
 int Sim::reset_state() {
     // a deposit of the previous population may still sit in either grid: both boxes bound it
-    for (int g = 0; g < kGrids; ++g)
-        if (grid[g]) k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[g], g);
+    for (int g = 0; g < kGrids; ++g)      // peer mode: boxes 0/1 describe this rank's own grids of the two exchange parities
+        k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, (peer_connected && g < 2) ? own_peer_grid(g) : grid[g], g);
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
     k_reset_bbox<<<1, 32, 0, stream>>>(st, kGrids);
     CK_LAST("Reset state");
@@ -571,7 +579,7 @@ int Sim::fused_steps(int steps) {
     const int per_launch = (cfg.nranks > 1 && !peer) ? 1 : steps;
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
-        FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2], grid[3]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
+        FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
@@ -814,7 +822,7 @@ int picb200_get_profile(picb200_sim* sim, picb200_profile* out) {
 int picb200_flush_l2(picb200_sim* sim) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
-    CK(cudaMemsetAsync(s.grid[(s.cur + 1) % (s.cfg.nranks > 1 ? kGrids : kRot)], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
+    CK(cudaMemsetAsync(s.grid[(s.cur + 1) % kRot], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
     CK(cudaStreamSynchronize(s.stream), "Flush L2");
     return 0;
 }
@@ -866,9 +874,21 @@ int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3
     int* buf = nullptr;
     const size_t cells = (size_t)wx * wy * wz;
     CK(cudaMalloc(&buf, cells * 4), "Charge box");
-    k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.grid[s.cur], buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
-    cudaError_t e = cudaMemcpyAsync(out, buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+    cudaError_t e = cudaSuccess;
+    if (s.peer_connected) {             // one grid per rank at the current parity: add them up on the host
+        std::vector<int32_t> tmp(cells);
+        std::fill(out, out + cells, 0);
+        for (int q = 0; q < s.cfg.nranks && e == cudaSuccess; ++q) {
+            k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.recv + ((size_t)((s.cur & 1) * s.cfg.nranks + q) << kCellsLog2), buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
+            e = cudaMemcpyAsync(tmp.data(), buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+            for (size_t k = 0; k < cells; ++k) out[k] += tmp[k];
+        }
+    } else {
+        k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.grid[s.cur], buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
+        e = cudaMemcpyAsync(out, buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+    }
     cudaFree(buf);
     CK(e, "Charge box");
     return 0;

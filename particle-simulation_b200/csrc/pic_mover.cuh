@@ -395,10 +395,11 @@ __device__ __forceinline__ void deposit_lanes(int* __restrict__ grid, bool activ
 
 // Grid-wide barrier; the last block to arrive runs `action` (one thread) before everyone is released.
 template <class F>
-__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action) {
+__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action, bool sys_scope = false) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence();
+        if (sys_scope) __threadfence_system();      // this block's stores into the peers' memory, too
+        else __threadfence();
         const unsigned target = (seq + 1u) * gridDim.x;
         const unsigned prev = atomicAdd(&st->bar_count, 1u);
         if (prev + 1u == target) {
@@ -417,12 +418,44 @@ __device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F acti
 
 struct FusedCtx {
     const float* bnd;
+    int nsrc;         // grids to add up in the gather: 1, or one per rank (consecutive 512^3 grids after A)
     int* A;
     int* B;
     int* s_box;
     double efc;
     bool store_acc;   // last Poisson step of this launch: the frozen acceleration becomes visible to the host
 };
+
+
+// updateGrid + gridToParticles for one electron's own cell (src/grid_operations.cu:29-72):
+// acc = float(EFC * double(c+ - c-)), absent neighbours at the domain faces count 0.  With several
+// ranks the counts are the sums over the per-rank grids (integer adds: any order, same result).
+__device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, int iz, float& ax, float& ay, float& az) {
+    int dx = 0, dy = 0, dz = 0;
+    const int* q = f.A + cell_index(ix, iy, iz);
+    const bool bx0 = ix != 0, bx1 = ix != kGrid - 1, by0 = iy != 0, by1 = iy != kGrid - 1, bz0 = iz != 0, bz1 = iz != kGrid - 1;
+    // four source grids per round, all 24 loads in flight before the first add (one L2 round trip for up
+    // to four ranks, two for eight); a loop over the ranks with one grid per iteration cost 11 us per step
+    for (int s0 = 0; s0 < f.nsrc; s0 += 4) {
+        int v[4][6];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const bool on = s0 + u < f.nsrc;
+            const int* g = q + ((size_t)(s0 + u) << kCellsLog2);
+            v[u][0] = (on && bx0) ? __ldcg(g - 1) : 0;
+            v[u][1] = (on && bx1) ? __ldcg(g + 1) : 0;
+            v[u][2] = (on && by0) ? __ldcg(g - kGrid) : 0;
+            v[u][3] = (on && by1) ? __ldcg(g + kGrid) : 0;
+            v[u][4] = (on && bz0) ? __ldcg(g - kGrid * kGrid) : 0;
+            v[u][5] = (on && bz1) ? __ldcg(g + kGrid * kGrid) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { dx += v[u][1] - v[u][0]; dy += v[u][3] - v[u][2]; dz += v[u][5] - v[u][4]; }
+    }
+    ax = __double2float_rn(__dmul_rn(f.efc, (double)dx));
+    ay = __double2float_rn(__dmul_rn(f.efc, (double)dy));
+    az = __double2float_rn(__dmul_rn(f.efc, (double)dz));
+}
 
 // generation-0 chunk of the fused kernel: gather from A, push, deposit into B
 template <bool kLaterGen>
@@ -442,13 +475,7 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
     if (!kLaterGen && was_alive) {
         // updateGrid + gridToParticles for this electron's own cell (src/grid_operations.cu:29-72)
         const int ix = cell_of_fast(e.x, f.bnd), iy = cell_of_fast(e.y, f.bnd), iz = cell_of_fast(e.z, f.bnd);
-        const int* q = f.A + cell_index(ix, iy, iz);
-        const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
-        const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
-        const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
-        e.ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
-        e.ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
-        e.az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
+        gather_field(f, ix, iy, iz, e.ax, e.ay, e.az);
         if (f.store_acc) { __stcg(c.s.ax + i, e.ax); __stcg(c.s.ay + i, e.ay); __stcg(c.s.az + i, e.az); }
     }
     bool alive = was_alive;
@@ -493,13 +520,7 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
     const float x0 = x, y0 = y, z0 = z;
     int ix = cell_of_fast(x, f.bnd), iy = cell_of_fast(y, f.bnd), iz = cell_of_fast(z, f.bnd);
     if (in) {
-        const int* q = f.A + cell_index(ix, iy, iz);
-        const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
-        const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
-        const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
-        ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
-        ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
-        az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
+        gather_field(f, ix, iy, iz, ax, ay, az);
         if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
     }
     const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
@@ -596,7 +617,7 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
 
 constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
-constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * kStageBytesPerWarp; }
+constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPushStageBytesPerWarp); }
 
 template <bool kPeer>
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
@@ -634,52 +655,62 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     unsigned seq = 0;
     const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
     unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
+    int* const push_stage = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPushSegCells;
+    f.nsrc = 1;
+    // the bookkeeping one thread does once an exchange is complete on this rank
+    auto peer_commit = [&](unsigned e) {
+        const int p = (int)(e & 1u);
+        volatile DevState* v = st;
+        volatile PeerLocal* pl = a.peer.pl;
+        for (int k = 0; k < 3; ++k) { pl->pbox_lo[p][k] = v->bbox_lo[p][k]; pl->pbox_hi[p][k] = v->bbox_hi[p][k]; }
+        pl->xseq = e;
+        v->cur = p;
+    };
     if (kPeer) {
+        f.nsrc = a.peer.nranks;
         xe = ld_sys_u32(&a.peer.pl->xseq);
         if (a.initial_deposit) {
-            // particlesToGrid of the first Poisson step for a fresh population: local deposit, exchange, sum
+            // particlesToGrid of the first Poisson step for a fresh population: local deposit, push, flags
             const unsigned e = xe + 1u;
-            const int lg = (int)(e & 1u);
+            const int p = (int)(e & 1u);
+            int* mine = peer_grid(a.peer, a.peer.rank, p, a.peer.rank);
             const int n = min(ld_volatile_i32(&st->n), a.capacity);
             const int rounded = (n + 31) & ~31;
             for (int i = (gwarp << 5) + c.lane; i < rounded; i += nwarp << 5) {
                 const bool in = i < n;
                 const float px = in ? __ldcg(c.s.x + i) : 0.f, py = in ? __ldcg(c.s.y + i) : 0.f, pz = in ? __ldcg(c.s.z + i) : 0.f;
-                deposit_lanes(a.grid[lg], in, cell_of_fast(px, f.bnd), cell_of_fast(py, f.bnd), cell_of_fast(pz, f.bnd), c.lane, s_box);
+                deposit_lanes(mine, in, cell_of_fast(px, f.bnd), cell_of_fast(py, f.bnd), cell_of_fast(pz, f.bnd), c.lane, s_box);
             }
             __syncthreads();
             if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
-                atomicMin(&st->bbox_lo[lg][threadIdx.x], s_box[threadIdx.x]);
-                atomicMax(&st->bbox_hi[lg][threadIdx.x], s_box[3 + threadIdx.x]);
+                atomicMin(&st->bbox_lo[p][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[p][threadIdx.x], s_box[3 + threadIdx.x]);
             }
-            grid_barrier(st, seq, [&]() { peer_exchange_boxes(st, a.peer, lg, e); });
-            {
-                PeerPull pp;
-                peer_pull_issue(st, a.peer, lg, 2 + lg, gwarp, c.lane, pp);
-                peer_pull_finish(a.peer, lg, a.grid[2 + lg], gwarp, nwarp, c.lane, pp);
-            }
+            grid_barrier(st, seq, []() {});
+            peer_push_rows(st, a.peer, p, gwarp, nwarp, c.lane, push_stage);
+            peer_push_drain(c.lane);
             if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
             grid_barrier(st, seq, [&]() {
-                volatile DevState* v = st;
-                for (int k = 0; k < 3; ++k) { v->bbox_lo[2 + lg][k] = v->xbox_lo[k]; v->bbox_hi[2 + lg][k] = v->xbox_hi[k]; }
-                v->cur = 2 + lg;
-                st_sys_u32(&a.peer.pl->xseq, e);
-                if (a.steps == 0) peer_finish(a.peer, e);
-            });
+                peer_signal(a.peer, e);
+                peer_wait(a.peer, e);
+                peer_commit(e);
+            }, true);
             xe = e;
         }
     }
     for (int step = 0; step < a.steps; ++step) {
         if (ld_volatile_i32(&st->hit_zero)) break;          // uniform: set before the previous barrier 3 released
         const int cur = ld_volatile_i32(&st->cur);
-        // single GPU: three grids in rotation.  Peer mode: gather from the summed grid of exchange xe,
-        // deposit into local grid (xe+1)&1, whose sum over the ranks lands in grid 2+((xe+1)&1).
+        // single GPU: three grids in rotation (gather / next deposit / being emptied).
+        // Peer mode: parity xe&1 holds the complete exchange xe -- one grid per rank, added up by the
+        // gather -- and this rank deposits into its own grid of the other parity.
         const int nxt = kPeer ? (int)((xe + 1u) & 1u) : (cur + 1) % kRot;
         const int old = kPeer ? (int)(xe & 1u) : (cur + 2) % kRot;
-        f.A = a.grid[cur];       // gathered from
-        f.B = a.grid[nxt];       // receives the (local) deposit of the next Poisson step
-                                 // a.grid[old]: single GPU: gathered from one step ago, emptied below;
-                                 // peer mode: the local deposit of the previous exchange, emptied after the next
+        f.A = kPeer ? peer_grid(a.peer, a.peer.rank, old, 0) : a.grid[cur];                 // gathered from
+        f.B = kPeer ? peer_grid(a.peer, a.peer.rank, nxt, a.peer.rank) : a.grid[nxt];       // (local) deposit of the next step
+        int* const g_old = kPeer ? peer_grid(a.peer, a.peer.rank, old, a.peer.rank) : a.grid[old];
+        // g_old: single GPU: gathered from one step ago, emptied during this step's main phase;
+        //        peer mode: this rank's own deposit of exchange xe, emptied once this step's gathers are done
         c.g0 = (unsigned)ld_volatile_i32(&st->poisson_index) * (unsigned)a.pt;
         const int n0 = min(ld_volatile_i32(&st->n), c.cap);
         const int chunks = (n0 + 31) >> 5;
@@ -703,7 +734,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         while (staged) fused_staged(c, f, staged, pushes, dead);
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
-        if (!kPeer) clear_box_rows(st, a.grid[old], old, gwarp, nwarp, c.lane);
+        if (!kPeer) clear_box_rows(st, g_old, old, gwarp, nwarp, c.lane);
         PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
         // ---- barrier 1 (+ fall-back passes over spilled children)
@@ -733,8 +764,6 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 const int unfinished = ld_volatile_i32(&st->n_unfinished);
                 st->n_unfinished = 0;
                 st->gen_hi = unfinished > 0 ? min(ld_volatile_i32(&st->n_alloc), c.cap) : -1;
-                // every local deposit of this step is in place: meet the other ranks
-                if (kPeer && unfinished <= 0) peer_exchange_boxes(st, a.peer, nxt, xe + 1u);
             });
             const int hi = ld_volatile_i32(&st->gen_hi);
             if (hi < 0) break;
@@ -749,25 +778,23 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
 
         // ---- every push of this step is done: list the holes and movers
         PIC_TRACE(3);          // barrier 1 passed
-        PeerPull pp;
         if (kPeer) {
-            // sum of all ranks' local grids -> the grid the next step gathers from: the loads over NVLink
-            // start here and are consumed after the compaction scan.  Nobody pulls from the previous
-            // local grid any more (every rank has passed the exchange above), so empty it.
-            peer_pull_issue(st, a.peer, nxt, 2 + nxt, gwarp, c.lane, pp);
+            // every local deposit of this step is in place: push this rank's box into its slot on every
+            // peer (posted stores over NVLink, nobody waits for them here), and empty this rank's own
+            // grid of the previous exchange, which only this step's gathers still needed
+            peer_push_rows(st, a.peer, nxt, gwarp, nwarp, c.lane, push_stage);
             PIC_TRACE(11);
-            clear_box_rows(st, a.grid[old], old, gwarp, nwarp, c.lane);
+            clear_box_rows(st, g_old, old, gwarp, nwarp, c.lane);
         }
         PIC_TRACE(8);
         compact_scan_body(c.s, st, c.cap, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
-        if (kPeer) peer_pull_finish(a.peer, nxt, a.grid[2 + nxt], gwarp, nwarp, c.lane, pp);
-        PIC_TRACE(12);
         PIC_TRACE(4);
         grid_barrier(st, seq, []() {});
         PIC_TRACE(5);
         compact_move_body(c.s, st, a.holes, a.movers);
         if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
         if (threadIdx.x == 0) s_ticket = 0;
+        if (kPeer) peer_push_drain(c.lane);          // the pushes have had the whole compaction to cross NVLink
         PIC_TRACE(6);
         // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
         grid_barrier(st, seq, [&]() {
@@ -775,10 +802,9 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             volatile DevState* v = st;
             for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
             if (kPeer) {
-                for (int k = 0; k < 3; ++k) { v->bbox_lo[2 + nxt][k] = v->xbox_lo[k]; v->bbox_hi[2 + nxt][k] = v->xbox_hi[k]; }
-                v->cur = 2 + nxt;
-                st_sys_u32(&a.peer.pl->xseq, xe + 1u);
-                if (step == a.steps - 1) peer_finish(a.peer, xe + 1u);
+                peer_signal(a.peer, xe + 1u);        // every block drained and fenced its bulk stores before arriving
+                peer_wait(a.peer, xe + 1u);          // the peers' slots of this exchange are complete here
+                peer_commit(xe + 1u);
             } else {
                 v->cur = nxt;
             }

@@ -13,7 +13,7 @@ print(f"{t.shape[0]} steps x {blocks} blocks; step time (first start -> last end
 for k, nm in enumerate(names):
     d = (t[:, :, k + 1] - t[:, :, k]) / 1e3
     print(f"  {nm:40s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
-for nm, a, b in (("peer: issue pull (3->11)", 3, 11), ("peer: clear old local grid (11->8)", 11, 8), ("peer: finish pull (after scan, ->12)", 8, 12), ("peer pull + clear (3->8)", 3, 8), ("scan: counters + ts loads + masks (8->9)", 8, 9), ("scan: block reserve (9->10)", 9, 10), ("scan: list stores (10->4)", 10, 4)):
+for nm, a, b in (("peer: push rows to the peers (3->11)", 3, 11), ("peer: clear own old grid (11->8)", 11, 8), ("scan: counters + ts loads + masks (8->9)", 8, 9), ("scan: block reserve (9->10)", 9, 10), ("scan: list stores (10->4)", 10, 4)):
     if t[:, :, a].min() > 0 and t[:, :, b].min() > 0:
         d = (t[:, :, b] - t[:, :, a]) / 1e3
         print(f"    {nm:40s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
