@@ -44,6 +44,7 @@ struct DevState {
     int gen_hi;             // end of the fall-back window agreed at the barrier (-1: none)
     int n_unfinished;       // children spilled to the global store before they were pushed to the end
     int bbox_lo[kGrids][3], bbox_hi[kGrids][3];  // cell bounding box of the counts deposited in each charge grid
+    int xbox_lo[3], xbox_hi[3];  // multi-GPU peer mode: union over the ranks of the boxes of the last exchange
     int cur;                // which of the charge grids holds the current deposit
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)
@@ -220,10 +221,9 @@ __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ char
 
 // K_clear: resetGrid (src/grid_operations.cu:6-12) restricted to the deposited bounding box.
 // Warp-granular form for the fused kernel: global warp `gw` of `nw` empties its x-rows of the box.
-__device__ __forceinline__ void clear_box_rows(const DevState* st, int* __restrict__ charge, int which, int gw, int nw, int lane) {
-    const int lx = __ldcg(&st->bbox_lo[which][0]), ly = __ldcg(&st->bbox_lo[which][1]), lz = __ldcg(&st->bbox_lo[which][2]);
-    const int wx = __ldcg(&st->bbox_hi[which][0]) - lx + 1, wy = __ldcg(&st->bbox_hi[which][1]) - ly + 1,
-              wz = __ldcg(&st->bbox_hi[which][2]) - lz + 1;
+__device__ __forceinline__ void clear_box_rows(int* __restrict__ charge, const int* box /* lo xyz, hi xyz */, int gw, int nw, int lane) {
+    const int lx = box[0], ly = box[1], lz = box[2];
+    const int wx = box[3] - lx + 1, wy = box[4] - ly + 1, wz = box[5] - lz + 1;
     if (wx <= 0 || wy <= 0 || wz <= 0) return;
     const int rows = wy * wz;
     for (int r = gw; r < rows; r += nw) {
@@ -283,7 +283,7 @@ __global__ void k_pack_box(const int* __restrict__ charge, int* __restrict__ buf
 // (warp-aggregated appends), pass 2 copies mover k into hole k.  Traffic is proportional to
 // the number of dead electrons, not to n, and no second capacity-sized buffer exists.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers,
+__device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, int S, int D, int* __restrict__ holes, int* __restrict__ movers,
                                                   unsigned long long* trace = nullptr) {
     // Every block owns a contiguous range of 128-slot "quads" (one int4 of timestamps per lane).  A warp
     // loads up to kScanDepth quads back to back (all loads in flight at once), keeps the hole / mover
@@ -293,8 +293,8 @@ __device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, in
     constexpr int kScanDepth = 8;
     __shared__ int s_cnt[2][32];
     __shared__ int s_base[2];
-    const int S = min(ld_volatile_i32(&st->n_alloc), capacity);
-    const int D = ld_volatile_i32(&st->n_dead);
+    // S = slots in use, D = dead among them: read ONCE per block by the caller (every thread asking L2 for
+    // the same word made that one L2 slice the bottleneck of the phase)
     if (D == 0) return;                                       // uniform over the grid
     const int L = S - D;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -354,10 +354,9 @@ __device__ __forceinline__ void compact_scan_body(const Soa& s, DevState* st, in
     }
 }
 __global__ void k_compact_scan(Soa s, DevState* st, int capacity, int* __restrict__ holes, int* __restrict__ movers) {
-    compact_scan_body(s, st, capacity, holes, movers);
+    compact_scan_body(s, st, min(ld_volatile_i32(&st->n_alloc), capacity), ld_volatile_i32(&st->n_dead), holes, movers);
 }
-__device__ __forceinline__ void compact_move_body(const Soa& s, const DevState* st, const int* holes, const int* movers) {
-    const int H = min(ld_volatile_i32(&st->n_holes), ld_volatile_i32(&st->n_movers));
+__device__ __forceinline__ void compact_move_body(const Soa& s, int H, const int* holes, const int* movers) {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < H; k += gridDim.x * blockDim.x) {
         const int src = __ldcg(movers + k), dst = __ldcg(holes + k);
         __stcg(s.x + dst, __ldcg(s.x + src)); __stcg(s.y + dst, __ldcg(s.y + src)); __stcg(s.z + dst, __ldcg(s.z + src));
@@ -368,7 +367,7 @@ __device__ __forceinline__ void compact_move_body(const Soa& s, const DevState* 
     }
 }
 __global__ void k_compact_move(Soa s, const DevState* st, const int* __restrict__ holes, const int* __restrict__ movers) {
-    compact_move_body(s, st, holes, movers);
+    compact_move_body(s, min(ld_volatile_i32(&st->n_holes), ld_volatile_i32(&st->n_movers)), holes, movers);
 }
 
 // Bookkeeping the reference does on the host after each phase (src/pic.cu:539-559), on the device.

@@ -406,8 +406,8 @@ int Sim::sync_state() {
 // A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
 int Sim::reset_state() {
     // a deposit of the previous population may still sit in either grid: both boxes bound it
-    for (int g = 0; g < kGrids; ++g)      // peer mode: boxes 0/1 describe this rank's own grids of the two exchange parities
-        k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, (peer_connected && g < 2) ? own_peer_grid(g) : grid[g], g);
+    for (int g = 0; g < kGrids; ++g)      // peer mode: boxes 0/1 = this rank's own grids of the two exchange parities, box 2 = the summed grid (grid 0)
+        k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, peer_connected ? (g < 2 ? own_peer_grid(g) : grid[0]) : grid[g], g);
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
     k_reset_bbox<<<1, 32, 0, stream>>>(st, kGrids);
     CK_LAST("Reset state");
@@ -874,21 +874,9 @@ int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3
     int* buf = nullptr;
     const size_t cells = (size_t)wx * wy * wz;
     CK(cudaMalloc(&buf, cells * 4), "Charge box");
-    cudaError_t e = cudaSuccess;
-    if (s.peer_connected) {             // one grid per rank at the current parity: add them up on the host
-        std::vector<int32_t> tmp(cells);
-        std::fill(out, out + cells, 0);
-        for (int q = 0; q < s.cfg.nranks && e == cudaSuccess; ++q) {
-            k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.recv + ((size_t)((s.cur & 1) * s.cfg.nranks + q) << kCellsLog2), buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
-            e = cudaMemcpyAsync(tmp.data(), buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
-            for (size_t k = 0; k < cells; ++k) out[k] += tmp[k];
-        }
-    } else {
-        k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.grid[s.cur], buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
-        e = cudaMemcpyAsync(out, buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
-    }
+    k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.grid[s.cur], buf, lo[0], lo[1], lo[2], wx, wy, wz, 0);
+    cudaError_t e = cudaMemcpyAsync(out, buf, cells * 4, cudaMemcpyDeviceToHost, s.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
     cudaFree(buf);
     CK(e, "Charge box");
     return 0;

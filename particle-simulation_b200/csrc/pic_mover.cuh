@@ -394,8 +394,8 @@ __device__ __forceinline__ void deposit_lanes(int* __restrict__ grid, bool activ
 }
 
 // Grid-wide barrier; the last block to arrive runs `action` (one thread) before everyone is released.
-template <class F>
-__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action, bool sys_scope = false) {
+template <class F, class G>
+__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action, G fetch, bool sys_scope = false) {
     __syncthreads();
     if (threadIdx.x == 0) {
         if (sys_scope) __threadfence_system();      // this block's stores into the peers' memory, too
@@ -411,14 +411,28 @@ __device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F acti
             while (ld_acquire_u32(&st->bar_release) < seq + 1u) __nanosleep(32);
         }
         __threadfence();
+        fetch();        // ONE thread per block reads what the next phase needs and leaves it in shared memory
     }
     ++seq;
     __syncthreads();
 }
+template <class F>
+__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action) {
+    grid_barrier(st, seq, action, []() {});
+}
+
+// What one thread per block reads from the control block after a grid barrier, for the whole block.
+struct BlockBc {
+    int hit_zero, cur, pidx, n;     // start of a Poisson step
+    int gen_hi, S, D;               // after barrier 1
+    int H;                          // after barrier 2
+    int box_old[6];                 // box of the grid this step empties (lo xyz, hi xyz)
+    int box_new[6], box_pushed[6];  // peer mode: box of this step's own deposit; box last pushed at that parity
+    int box_union[6], box_sum[6];   // peer mode: union of the ranks' boxes of the last exchange; box the summed grid still holds
+};
 
 struct FusedCtx {
     const float* bnd;
-    int nsrc;         // grids to add up in the gather: 1, or one per rank (consecutive 512^3 grids after A)
     int* A;
     int* B;
     int* s_box;
@@ -428,33 +442,15 @@ struct FusedCtx {
 
 
 // updateGrid + gridToParticles for one electron's own cell (src/grid_operations.cu:29-72):
-// acc = float(EFC * double(c+ - c-)), absent neighbours at the domain faces count 0.  With several
-// ranks the counts are the sums over the per-rank grids (integer adds: any order, same result).
+// acc = float(EFC * double(c+ - c-)), absent neighbours at the domain faces count 0.
 __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, int iz, float& ax, float& ay, float& az) {
-    int dx = 0, dy = 0, dz = 0;
     const int* q = f.A + cell_index(ix, iy, iz);
-    const bool bx0 = ix != 0, bx1 = ix != kGrid - 1, by0 = iy != 0, by1 = iy != kGrid - 1, bz0 = iz != 0, bz1 = iz != kGrid - 1;
-    // four source grids per round, all 24 loads in flight before the first add (one L2 round trip for up
-    // to four ranks, two for eight); a loop over the ranks with one grid per iteration cost 11 us per step
-    for (int s0 = 0; s0 < f.nsrc; s0 += 4) {
-        int v[4][6];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const bool on = s0 + u < f.nsrc;
-            const int* g = q + ((size_t)(s0 + u) << kCellsLog2);
-            v[u][0] = (on && bx0) ? __ldcg(g - 1) : 0;
-            v[u][1] = (on && bx1) ? __ldcg(g + 1) : 0;
-            v[u][2] = (on && by0) ? __ldcg(g - kGrid) : 0;
-            v[u][3] = (on && by1) ? __ldcg(g + kGrid) : 0;
-            v[u][4] = (on && bz0) ? __ldcg(g - kGrid * kGrid) : 0;
-            v[u][5] = (on && bz1) ? __ldcg(g + kGrid * kGrid) : 0;
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { dx += v[u][1] - v[u][0]; dy += v[u][3] - v[u][2]; dz += v[u][5] - v[u][4]; }
-    }
-    ax = __double2float_rn(__dmul_rn(f.efc, (double)dx));
-    ay = __double2float_rn(__dmul_rn(f.efc, (double)dy));
-    az = __double2float_rn(__dmul_rn(f.efc, (double)dz));
+    const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
+    const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
+    const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
+    ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
+    ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
+    az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
 }
 
 // generation-0 chunk of the fused kernel: gather from A, push, deposit into B
@@ -626,6 +622,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
     __shared__ unsigned long long s_pushes;
     __shared__ int s_dead;
+    __shared__ BlockBc bc;
     if (threadIdx.x == 0) { s_ticket = 0; s_pushes = 0; s_dead = 0; }
     {
         const float4* src = reinterpret_cast<const float4*>(a.tables);
@@ -656,18 +653,49 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
     unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
     int* const push_stage = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPushSegCells;
-    f.nsrc = 1;
+    volatile DevState* const v = st;
+
+    // ---- what ONE thread per block fetches after each grid barrier (BlockBc): every thread asking L2 for
+    // the same control words made that one L2 slice the bottleneck of the short phases
+    auto load_box = [&](int* dst, const volatile int* lo, const volatile int* hi) {
+        for (int k = 0; k < 3; ++k) { dst[k] = lo[k]; dst[3 + k] = hi[k]; }
+    };
+    auto fetch_step_start = [&](unsigned e_done) {           // e_done: exchanges complete (peer mode)
+        bc.hit_zero = v->hit_zero; bc.cur = v->cur; bc.pidx = v->poisson_index; bc.n = v->n;
+        const int old = kPeer ? (int)(e_done & 1u) : (bc.cur + 2) % kRot;
+        load_box(bc.box_old, v->bbox_lo[old], v->bbox_hi[old]);
+        if (kPeer) { load_box(bc.box_union, v->xbox_lo, v->xbox_hi); load_box(bc.box_sum, v->bbox_lo[2], v->bbox_hi[2]); }
+    };
+    auto fetch_after_b1 = [&](int nxt) {
+        bc.gen_hi = v->gen_hi; bc.S = min(v->n_alloc, a.capacity); bc.D = v->n_dead;
+        if (kPeer) {
+            volatile PeerLocal* pl = a.peer.pl;
+            load_box(bc.box_new, v->bbox_lo[nxt], v->bbox_hi[nxt]);
+            load_box(bc.box_pushed, pl->pbox_lo[nxt], pl->pbox_hi[nxt]);
+        }
+    };
+    auto fetch_after_b2 = [&]() { bc.H = min(v->n_holes, v->n_movers); };
     // the bookkeeping one thread does once an exchange is complete on this rank
-    auto peer_commit = [&](unsigned e) {
+    auto peer_commit = [&](unsigned e) {                     // ONE thread, every block's pushes drained and fenced
         const int p = (int)(e & 1u);
-        volatile DevState* v = st;
         volatile PeerLocal* pl = a.peer.pl;
-        for (int k = 0; k < 3; ++k) { pl->pbox_lo[p][k] = v->bbox_lo[p][k]; pl->pbox_hi[p][k] = v->bbox_hi[p][k]; }
+        int lo[3], hi[3];
+        for (int k = 0; k < 3; ++k) { lo[k] = v->bbox_lo[p][k]; hi[k] = v->bbox_hi[p][k]; }
+        peer_signal(a.peer, e, lo, hi);
+        for (int k = 0; k < 3; ++k) { pl->pbox_lo[p][k] = lo[k]; pl->pbox_hi[p][k] = hi[k]; }
+        peer_wait(a.peer, e, lo, hi);                        // the peers' slots of this exchange are complete here
+        for (int k = 0; k < 3; ++k) { v->xbox_lo[k] = lo[k]; v->xbox_hi[k] = hi[k]; }
         pl->xseq = e;
-        v->cur = p;
+        v->cur = 0;                                          // grid 0 = the sum over the ranks (box: bbox[2])
+    };
+    // all warps, after peer_commit: per-rank slots -> the one grid the next step gathers from, then a barrier
+    auto peer_sum = [&](unsigned e) {
+        peer_sum_rows(a.peer, (int)(e & 1u), a.grid[0], bc.box_union, bc.box_sum, gwarp, nwarp, c.lane);
+        grid_barrier(st, seq, [&]() {
+            for (int k = 0; k < 3; ++k) { v->bbox_lo[2][k] = v->xbox_lo[k]; v->bbox_hi[2][k] = v->xbox_hi[k]; }
+        }, [&]() { load_box(bc.box_sum, v->xbox_lo, v->xbox_hi); });
     };
     if (kPeer) {
-        f.nsrc = a.peer.nranks;
         xe = ld_sys_u32(&a.peer.pl->xseq);
         if (a.initial_deposit) {
             // particlesToGrid of the first Poisson step for a fresh population: local deposit, push, flags
@@ -686,33 +714,34 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 atomicMin(&st->bbox_lo[p][threadIdx.x], s_box[threadIdx.x]);
                 atomicMax(&st->bbox_hi[p][threadIdx.x], s_box[3 + threadIdx.x]);
             }
-            grid_barrier(st, seq, []() {});
-            peer_push_rows(st, a.peer, p, gwarp, nwarp, c.lane, push_stage);
+            grid_barrier(st, seq, []() {}, [&]() { fetch_after_b1(p); });
+            peer_push_rows(a.peer, p, bc.box_new, bc.box_pushed, gwarp, nwarp, c.lane, push_stage);
             peer_push_drain(c.lane);
             if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
-            grid_barrier(st, seq, [&]() {
-                peer_signal(a.peer, e);
-                peer_wait(a.peer, e);
-                peer_commit(e);
-            }, true);
+            grid_barrier(st, seq, [&]() { peer_commit(e); }, [&]() { fetch_step_start(e); }, true);
+            peer_sum(e);
             xe = e;
         }
     }
+    if (!(kPeer && a.initial_deposit)) {                     // no barrier has filled the block's copy yet
+        if (threadIdx.x == 0) fetch_step_start(xe);
+        __syncthreads();
+    }
     for (int step = 0; step < a.steps; ++step) {
-        if (ld_volatile_i32(&st->hit_zero)) break;          // uniform: set before the previous barrier 3 released
-        const int cur = ld_volatile_i32(&st->cur);
+        if (bc.hit_zero) break;                              // uniform: set before the previous barrier 3 released
+        const int cur = bc.cur;
         // single GPU: three grids in rotation (gather / next deposit / being emptied).
-        // Peer mode: parity xe&1 holds the complete exchange xe -- one grid per rank, added up by the
-        // gather -- and this rank deposits into its own grid of the other parity.
+        // Peer mode: grid 0 holds the sum over the ranks of exchange xe; this rank deposits into its own
+        // grid of parity (xe+1)&1, pushes it to the peers, and the per-rank grids are added up after barrier 3.
         const int nxt = kPeer ? (int)((xe + 1u) & 1u) : (cur + 1) % kRot;
         const int old = kPeer ? (int)(xe & 1u) : (cur + 2) % kRot;
-        f.A = kPeer ? peer_grid(a.peer, a.peer.rank, old, 0) : a.grid[cur];                 // gathered from
+        f.A = kPeer ? a.grid[0] : a.grid[cur];                                              // gathered from (peer mode: the sum over the ranks)
         f.B = kPeer ? peer_grid(a.peer, a.peer.rank, nxt, a.peer.rank) : a.grid[nxt];       // (local) deposit of the next step
         int* const g_old = kPeer ? peer_grid(a.peer, a.peer.rank, old, a.peer.rank) : a.grid[old];
         // g_old: single GPU: gathered from one step ago, emptied during this step's main phase;
         //        peer mode: this rank's own deposit of exchange xe, emptied once this step's gathers are done
-        c.g0 = (unsigned)ld_volatile_i32(&st->poisson_index) * (unsigned)a.pt;
-        const int n0 = min(ld_volatile_i32(&st->n), c.cap);
+        c.g0 = (unsigned)bc.pidx * (unsigned)a.pt;
+        const int n0 = min(bc.n, c.cap);
         const int chunks = (n0 + 31) >> 5;
         int staged = 0;
         unsigned pushes = 0;
@@ -734,7 +763,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         while (staged) fused_staged(c, f, staged, pushes, dead);
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
-        if (!kPeer) clear_box_rows(st, g_old, old, gwarp, nwarp, c.lane);
+        if (!kPeer) clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
         PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
         // ---- barrier 1 (+ fall-back passes over spilled children)
@@ -761,11 +790,11 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 atomicMax(&st->bbox_hi[nxt][threadIdx.x], s_box[3 + threadIdx.x]);
             }
             grid_barrier(st, seq, [&]() {
-                const int unfinished = ld_volatile_i32(&st->n_unfinished);
-                st->n_unfinished = 0;
-                st->gen_hi = unfinished > 0 ? min(ld_volatile_i32(&st->n_alloc), c.cap) : -1;
-            });
-            const int hi = ld_volatile_i32(&st->gen_hi);
+                const int unfinished = v->n_unfinished;
+                v->n_unfinished = 0;
+                v->gen_hi = unfinished > 0 ? min(v->n_alloc, c.cap) : -1;
+            }, [&]() { fetch_after_b1(nxt); });
+            const int hi = bc.gen_hi;
             if (hi < 0) break;
             const int rounded = (hi - lo + 31) & ~31;
             for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x) {
@@ -779,19 +808,20 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // ---- every push of this step is done: list the holes and movers
         PIC_TRACE(3);          // barrier 1 passed
         if (kPeer) {
-            // every local deposit of this step is in place: push this rank's box into its slot on every
-            // peer (posted stores over NVLink, nobody waits for them here), and empty this rank's own
-            // grid of the previous exchange, which only this step's gathers still needed
-            peer_push_rows(st, a.peer, nxt, gwarp, nwarp, c.lane, push_stage);
+            // every local deposit of this step is in place: hand this rank's box to the copy engine for its
+            // slot on every peer (asynchronous bulk stores over NVLink), and empty this rank's own grid of
+            // the previous exchange, which only this step's gathers still needed
+            peer_push_rows(a.peer, nxt, bc.box_new, bc.box_pushed, gwarp, nwarp, c.lane, push_stage);
             PIC_TRACE(11);
-            clear_box_rows(st, g_old, old, gwarp, nwarp, c.lane);
+            clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
         }
         PIC_TRACE(8);
-        compact_scan_body(c.s, st, c.cap, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
+        const int scan_S = bc.S, scan_D = bc.D;              // (the scan's own __syncthreads separate these reads from the next fetch)
+        compact_scan_body(c.s, st, scan_S, scan_D, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
         PIC_TRACE(4);
-        grid_barrier(st, seq, []() {});
+        grid_barrier(st, seq, []() {}, fetch_after_b2);
         PIC_TRACE(5);
-        compact_move_body(c.s, st, a.holes, a.movers);
+        compact_move_body(c.s, bc.H, a.holes, a.movers);
         if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
         if (threadIdx.x == 0) s_ticket = 0;
         if (kPeer) peer_push_drain(c.lane);          // the pushes have had the whole compaction to cross NVLink
@@ -799,18 +829,13 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
         grid_barrier(st, seq, [&]() {
             step_end_body(st, c.cap, a.log, a.log_len, a.stop_at_zero);
-            volatile DevState* v = st;
             for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
-            if (kPeer) {
-                peer_signal(a.peer, xe + 1u);        // every block drained and fenced its bulk stores before arriving
-                peer_wait(a.peer, xe + 1u);          // the peers' slots of this exchange are complete here
-                peer_commit(xe + 1u);
-            } else {
-                v->cur = nxt;
-            }
+            if (kPeer) peer_commit(xe + 1u);
+            else v->cur = nxt;
             v->ticket = 0;
             v->n_unfinished = 0;
-        });
+        }, [&]() { fetch_step_start(xe + 1u); }, kPeer);
+        if (kPeer) peer_sum(xe + 1u);
         ++xe;
         PIC_TRACE(7);
     }

@@ -16,8 +16,10 @@
 constexpr int kMaxRanks = 8;
 constexpr int kCellsLog2 = 27;          // 512^3 cells per grid
 
-// One flag word per (exchange parity, source rank), written by the source rank into every peer's mailbox.
-struct alignas(16) PeerMsg { unsigned seq; unsigned pad[3]; };
+// One message per (exchange parity, source rank), written by the source rank into every peer's mailbox:
+// {box lo packed 3 x 10 bits, box hi likewise, exchange number, 0} in ONE 16-byte store, so the box can
+// never be seen without its sequence number (lo > hi on an axis: empty box).
+struct alignas(16) PeerMsg { uint4 box; };
 struct PeerMailbox { PeerMsg msg[2][kMaxRanks]; };
 
 // Survives picb200_upload / init (the exchange counter must never run backwards: peers compare it).
@@ -66,13 +68,11 @@ __device__ __forceinline__ void bulk_store_commit() { asm volatile("cp.async.bul
 __device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-__device__ __forceinline__ void peer_push_rows(const DevState* st, const PeerArgs& P, int p, int gw, int nw, int lane, int* stage /* smem, per warp */) {
+__device__ __forceinline__ void peer_push_rows(const PeerArgs& P, int p, const int* nbox, const int* obox /* lo xyz, hi xyz each */, int gw, int nw,
+                                               int lane, int* stage /* smem, per warp */) {
     int lo[3], hi[3], hl[3], hh[3];
     bool any = true, old_any = true;
-    for (int k = 0; k < 3; ++k) {
-        lo[k] = __ldcg(&st->bbox_lo[p][k]); hi[k] = __ldcg(&st->bbox_hi[p][k]);
-        hl[k] = __ldcg(&P.pl->pbox_lo[p][k]); hh[k] = __ldcg(&P.pl->pbox_hi[p][k]);
-    }
+    for (int k = 0; k < 3; ++k) { lo[k] = nbox[k]; hi[k] = nbox[3 + k]; hl[k] = obox[k]; hh[k] = obox[3 + k]; }
     for (int k = 0; k < 3; ++k) { any = any && lo[k] <= hi[k]; old_any = old_any && hl[k] <= hh[k]; }
     if (!any && !old_any) return;
     if (!old_any) { for (int k = 0; k < 3; ++k) { hl[k] = lo[k]; hh[k] = hi[k]; } }
@@ -106,27 +106,77 @@ __device__ __forceinline__ void peer_push_rows(const DevState* st, const PeerArg
         }
     }
 }
-// Every lane that issued bulk stores (lane 0 of each warp): wait until they are complete, then order them
-// before this block's arrival at the grid barrier at system scope.
+// Every lane that issued bulk stores (lane 0 of each warp): wait until they are complete.
 __device__ __forceinline__ void peer_push_drain(int lane) {
-    if (lane == 0) { bulk_store_wait_all(); __threadfence_system(); }
+    if (lane == 0) bulk_store_wait_all();       // (the grid barrier that follows fences once per block at system scope)
 }
 
-// ONE thread, after every block of this rank has fenced its pushes at system scope: tell the peers.
-__device__ __forceinline__ void peer_signal(const PeerArgs& P, unsigned e) {
+__device__ __forceinline__ void st_sys_v4(uint4* p, uint4 v) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_sys_v4(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+// ONE thread, after every block of this rank has drained its bulk stores and the barrier has fenced them at
+// system scope: tell the peers that this rank's slot of exchange `e` is complete, and which box it occupies.
+__device__ __forceinline__ void peer_signal(const PeerArgs& P, unsigned e, const int* lo, const int* hi) {
+    const bool mine = hi[0] >= lo[0];
+    const uint4 msg = make_uint4(mine ? (unsigned)(lo[0] | (lo[1] << 10) | (lo[2] << 20)) : 0x00100401u,   // empty: lo = 1, hi = 0
+                                 mine ? (unsigned)(hi[0] | (hi[1] << 10) | (hi[2] << 20)) : 0u, e, 0u);
     __threadfence_system();
     for (int r = 0; r < P.nranks; ++r)
-        if (r != P.rank) st_sys_u32(&P.mail[r]->msg[e & 1u][P.rank].seq, e);
+        if (r != P.rank) st_sys_v4(&P.mail[r]->msg[e & 1u][P.rank].box, msg);
 }
-// ONE thread: wait until every peer's slot of exchange `e` is complete in this rank's memory.
-__device__ __forceinline__ void peer_wait(const PeerArgs& P, unsigned e) {
+// ONE thread: wait until every peer's slot of exchange `e` is complete in this rank's memory; lo/hi come in
+// as this rank's box and leave as the union over the ranks.
+__device__ __forceinline__ void peer_wait(const PeerArgs& P, unsigned e, int* lo, int* hi) {
     const unsigned long long t0 = peer_timer_ns();
     for (int r = 0; r < P.nranks; ++r) {
         if (r == P.rank) continue;
         const PeerMsg* m = &P.mail[P.rank]->msg[e & 1u][r];
-        while ((int)(ld_sys_u32(&m->seq) - e) < 0) {
+        uint4 got = ld_sys_v4(&m->box);
+        while ((int)(got.z - e) < 0) {
             if (peer_timer_ns() - t0 > kPeerTimeoutNs) { P.pl->error = 1; break; }
+            got = ld_sys_v4(&m->box);
+        }
+        for (int k = 0; k < 3; ++k) {
+            const int pl = (int)((got.x >> (10 * k)) & 1023u), ph = (int)((got.y >> (10 * k)) & 1023u);
+            if (pl <= ph) { lo[k] = min(lo[k], pl); hi[k] = max(hi[k], ph); }
         }
     }
     __threadfence_system();
+}
+
+// All warps of the rank, once every slot of parity `p` is complete: add the per-rank grids up over the union
+// box into `sum_grid` (the one grid the next step gathers from -- six scattered loads per electron from one
+// grid, not from one per rank), writing zeros over what is left of its previous box; one warp per x-row.
+__device__ __forceinline__ void peer_sum_rows(const PeerArgs& P, int p, int* __restrict__ sum_grid, const int* ubox, const int* obox, int gw, int nw, int lane) {
+    int lo[3], hi[3], hl[3], hh[3];
+    bool any = true, old_any = true;
+    for (int k = 0; k < 3; ++k) { lo[k] = ubox[k]; hi[k] = ubox[3 + k]; hl[k] = obox[k]; hh[k] = obox[3 + k]; }
+    for (int k = 0; k < 3; ++k) { any = any && lo[k] <= hi[k]; old_any = old_any && hl[k] <= hh[k]; }
+    if (!any && !old_any) return;
+    if (!old_any) { for (int k = 0; k < 3; ++k) { hl[k] = lo[k]; hh[k] = hi[k]; } }
+    else if (any) { for (int k = 0; k < 3; ++k) { hl[k] = min(hl[k], lo[k]); hh[k] = max(hh[k], hi[k]); } }
+    const int wx = hh[0] - hl[0] + 1, wy = hh[1] - hl[1] + 1, wz = hh[2] - hl[2] + 1;
+    const int rows = wy * wz;
+    const int* slot0 = peer_grid(P, P.rank, p, 0);
+    for (int r = gw; r < rows; r += nw) {
+        const int y = hl[1] + r % wy, z = hl[2] + r / wy;
+        const bool row_in = any && y >= lo[1] && y <= hi[1] && z >= lo[2] && z <= hi[2];
+        const size_t base = cell_index(hl[0], y, z);
+        for (int xx = lane; xx < wx; xx += 32) {
+            const int x = hl[0] + xx;
+            int sum = 0;
+            if (row_in && x >= lo[0] && x <= hi[0]) {
+#pragma unroll
+                for (int q = 0; q < kMaxRanks; ++q)
+                    if (q < P.nranks) sum += __ldcg(slot0 + ((size_t)q << kCellsLog2) + base + xx);
+            }
+            __stcg(sum_grid + base + xx, sum);
+        }
+    }
 }
