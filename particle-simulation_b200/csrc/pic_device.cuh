@@ -44,7 +44,6 @@ struct DevState {
     int gen_hi;             // end of the fall-back window agreed at the barrier (-1: none)
     int n_unfinished;       // children spilled to the global store before they were pushed to the end
     int bbox_lo[kGrids][3], bbox_hi[kGrids][3];  // cell bounding box of the counts deposited in each charge grid
-    int xbox_lo[3], xbox_hi[3];  // multi-GPU peer mode: union over the ranks of the boxes of the last exchange
     int cur;                // which of the charge grids holds the current deposit
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)

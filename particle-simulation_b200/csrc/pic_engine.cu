@@ -116,8 +116,6 @@ struct Sim {
     int* h_bbox_red = nullptr;
     // multi-GPU, peer mode: the exchange runs inside the fused kernel over NVLink peer mappings
     PeerMailbox* mail = nullptr;         // written by the peers
-    int* recv = nullptr;                 // 2 parities x nranks grids: slot [p][rank] = own deposit, the others are written by the peers
-    int* own_peer_grid(int p) const { return recv + ((size_t)(p * cfg.nranks + cfg.rank) << kCellsLog2); }
     PeerLocal* pl = nullptr;
     PeerLocal* h_pl = nullptr;           // pinned mirror
     PeerArgs pa{};
@@ -199,7 +197,6 @@ void Sim::release() {
     for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
     ipc_opened.clear();
     cudaFree(mail); mail = nullptr;
-    cudaFree(recv); recv = nullptr;
     cudaFree(pl); pl = nullptr;
     if (h_pl) { cudaFreeHost(h_pl); h_pl = nullptr; }
     cudaFree(soa_base); soa_base = nullptr;
@@ -333,34 +330,28 @@ struct PeerHandle {
     unsigned magic;
     int device;
     long long pid;
-    void* raw[2];                    // block of 2 x nranks grids, mailbox
-    cudaIpcMemHandle_t ipc[2];
+    void* raw[3];                    // summed grid 0, summed grid 1, mailbox
+    cudaIpcMemHandle_t ipc[3];
 };
 static_assert(sizeof(PeerHandle) <= PICB200_PEER_HANDLE_BYTES, "handle fits the ABI blob");
 
 int Sim::peer_export(void* out) {
     if (cfg.nranks < 2 || !mail) return fail("peer export needs nranks > 1", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
-    if (!recv) {     // one grid per (parity, rank): 2 x nranks x 512 MiB, zeroed once, then kept zero outside the boxes
-        const size_t bytes = ((size_t)2 * (size_t)cfg.nranks << kCellsLog2) * sizeof(int);
-        CK(cudaMalloc(&recv, bytes), "Peer grid alloc");
-        CK(cudaMemsetAsync(recv, 0, bytes, stream), "Peer grid alloc");
-        CK(cudaStreamSynchronize(stream), "Peer grid alloc");
-    }
     PeerHandle h;
     memset(&h, 0, sizeof(h));
     h.magic = 0x50494342u;
     h.device = device;
     h.pid = (long long)getpid();
-    h.raw[0] = recv; h.raw[1] = mail;
-    for (int k = 0; k < 2; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
+    h.raw[0] = grid[0]; h.raw[1] = grid[1]; h.raw[2] = mail;
+    for (int k = 0; k < 3; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
     memset(out, 0, PICB200_PEER_HANDLE_BYTES);
     memcpy(out, &h, sizeof(h));
     return 0;
 }
 
 int Sim::peer_connect(const void* handles) {
-    if (cfg.nranks < 2 || !mail || !recv) return fail("peer connect needs nranks > 1 and a prior picb200_peer_export", "Peer setup");
+    if (cfg.nranks < 2 || !mail) return fail("peer connect needs nranks > 1", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
     memset(&pa, 0, sizeof(pa));
     pa.rank = cfg.rank;
@@ -370,9 +361,9 @@ int Sim::peer_connect(const void* handles) {
         PeerHandle h;
         memcpy(&h, static_cast<const unsigned char*>(handles) + (size_t)r * PICB200_PEER_HANDLE_BYTES, sizeof(h));
         if (h.magic != 0x50494342u) return fail("bad peer handle", "Peer setup");
-        void* p[2] = {nullptr, nullptr};
+        void* p[3] = {nullptr, nullptr, nullptr};
         if (r == cfg.rank) {
-            p[0] = recv; p[1] = mail;
+            p[0] = grid[0]; p[1] = grid[1]; p[2] = mail;
         } else if (h.pid == (long long)getpid()) {
             int can = 0;
             CK(cudaDeviceCanAccessPeer(&can, device, h.device), "Peer setup");
@@ -380,16 +371,19 @@ int Sim::peer_connect(const void* handles) {
             cudaError_t e = cudaDeviceEnablePeerAccess(h.device, 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(cudaGetErrorString(e), "Peer setup (enable peer access)");
             cudaGetLastError();
-            for (int k = 0; k < 2; ++k) p[k] = h.raw[k];
+            for (int k = 0; k < 3; ++k) p[k] = h.raw[k];
         } else {
-            for (int k = 0; k < 2; ++k) {
+            for (int k = 0; k < 3; ++k) {
                 CK(cudaIpcOpenMemHandle(&p[k], h.ipc[k], cudaIpcMemLazyEnablePeerAccess), "Peer setup (cudaIpcOpenMemHandle)");
                 ipc_opened.push_back(p[k]);
             }
         }
-        pa.recv[r] = static_cast<int*>(p[0]);
-        pa.mail[r] = static_cast<PeerMailbox*>(p[1]);
+        pa.sum[r][0] = static_cast<int*>(p[0]);
+        pa.sum[r][1] = static_cast<int*>(p[1]);
+        pa.mail[r] = static_cast<PeerMailbox*>(p[2]);
     }
+    // connect before the first population is created (the grids are still all-zero then)
+    if (charge_valid) return fail("picb200_peer_connect must precede the first Poisson step", "Peer setup");
     peer_connected = true;
     return 0;
 }
@@ -406,8 +400,10 @@ int Sim::sync_state() {
 // A fresh population starts a fresh run: counters, Poisson index and totals go back to zero.
 int Sim::reset_state() {
     // a deposit of the previous population may still sit in either grid: both boxes bound it
-    for (int g = 0; g < kGrids; ++g)      // peer mode: boxes 0/1 = this rank's own grids of the two exchange parities, box 2 = the summed grid (grid 0)
-        k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, peer_connected ? (g < 2 ? own_peer_grid(g) : grid[0]) : grid[g], g);
+    // peer mode: grids 0/1 are the summed grids the peers add into.  They are never touched from the host:
+    // the one that will receive the next exchange is already empty, the other one is emptied by the first
+    // Poisson step after its gathers (see pic_peer.cuh); only the local grid 2 is this rank's alone.
+    for (int g = peer_connected ? 2 : 0; g < kGrids; ++g) k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[g], g);
     CK(cudaMemsetAsync(st, 0, sizeof(DevState), stream), "Reset state");
     k_reset_bbox<<<1, 32, 0, stream>>>(st, kGrids);
     CK_LAST("Reset state");

@@ -427,8 +427,7 @@ struct BlockBc {
     int gen_hi, S, D;               // after barrier 1
     int H;                          // after barrier 2
     int box_old[6];                 // box of the grid this step empties (lo xyz, hi xyz)
-    int box_new[6], box_pushed[6];  // peer mode: box of this step's own deposit; box last pushed at that parity
-    int box_union[6], box_sum[6];   // peer mode: union of the ranks' boxes of the last exchange; box the summed grid still holds
+    int box_new[6];                 // peer mode: box of this step's own (local) deposit
 };
 
 struct FusedCtx {
@@ -664,36 +663,30 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         bc.hit_zero = v->hit_zero; bc.cur = v->cur; bc.pidx = v->poisson_index; bc.n = v->n;
         const int old = kPeer ? (int)(e_done & 1u) : (bc.cur + 2) % kRot;
         load_box(bc.box_old, v->bbox_lo[old], v->bbox_hi[old]);
-        if (kPeer) { load_box(bc.box_union, v->xbox_lo, v->xbox_hi); load_box(bc.box_sum, v->bbox_lo[2], v->bbox_hi[2]); }
     };
     auto fetch_after_b1 = [&](int nxt) {
         bc.gen_hi = v->gen_hi; bc.S = min(v->n_alloc, a.capacity); bc.D = v->n_dead;
-        if (kPeer) {
-            volatile PeerLocal* pl = a.peer.pl;
-            load_box(bc.box_new, v->bbox_lo[nxt], v->bbox_hi[nxt]);
-            load_box(bc.box_pushed, pl->pbox_lo[nxt], pl->pbox_hi[nxt]);
-        }
+        if (kPeer) load_box(bc.box_new, v->bbox_lo[nxt], v->bbox_hi[nxt]);
     };
     auto fetch_after_b2 = [&]() { bc.H = min(v->n_holes, v->n_movers); };
     // the bookkeeping one thread does once an exchange is complete on this rank
-    auto peer_commit = [&](unsigned e) {                     // ONE thread, every block's pushes drained and fenced
-        const int p = (int)(e & 1u);
-        volatile PeerLocal* pl = a.peer.pl;
+    // ONE thread, once every block has drained its bulk adds and the barrier has fenced them at system scope
+    auto peer_raise_flag = [&](unsigned e) {
         int lo[3], hi[3];
-        for (int k = 0; k < 3; ++k) { lo[k] = v->bbox_lo[p][k]; hi[k] = v->bbox_hi[p][k]; }
+        for (int k = 0; k < 3; ++k) { lo[k] = v->bbox_lo[2][k]; hi[k] = v->bbox_hi[2][k]; }
         peer_signal(a.peer, e, lo, hi);
-        for (int k = 0; k < 3; ++k) { pl->pbox_lo[p][k] = lo[k]; pl->pbox_hi[p][k] = hi[k]; }
-        peer_wait(a.peer, e, lo, hi);                        // the peers' slots of this exchange are complete here
-        for (int k = 0; k < 3; ++k) { v->xbox_lo[k] = lo[k]; v->xbox_hi[k] = hi[k]; }
-        pl->xseq = e;
-        v->cur = 0;                                          // grid 0 = the sum over the ranks (box: bbox[2])
     };
-    // all warps, after peer_commit: per-rank slots -> the one grid the next step gathers from, then a barrier
-    auto peer_sum = [&](unsigned e) {
-        peer_sum_rows(a.peer, (int)(e & 1u), a.grid[0], bc.box_union, bc.box_sum, gwarp, nwarp, c.lane);
-        grid_barrier(st, seq, [&]() {
-            for (int k = 0; k < 3; ++k) { v->bbox_lo[2][k] = v->xbox_lo[k]; v->bbox_hi[2][k] = v->xbox_hi[k]; }
-        }, [&]() { load_box(bc.box_sum, v->xbox_lo, v->xbox_hi); });
+    auto peer_commit = [&](unsigned e) {                     // ONE thread, after peer_raise_flag
+        const int p = (int)(e & 1u);
+        int lo[3], hi[3];
+        for (int k = 0; k < 3; ++k) { lo[k] = v->bbox_lo[2][k]; hi[k] = v->bbox_hi[2][k]; }      // box of this rank's local deposit
+        peer_wait(a.peer, e, lo, hi);                        // every rank's rows have been added into S[p] here
+        for (int k = 0; k < 3; ++k) {
+            v->bbox_lo[p][k] = lo[k]; v->bbox_hi[p][k] = hi[k];          // what S[p] now holds: the union box
+            v->bbox_lo[2][k] = kGrid; v->bbox_hi[2][k] = -1;             // the local grid was emptied on the way out
+        }
+        a.peer.pl->xseq = e;
+        v->cur = p;
     };
     if (kPeer) {
         xe = ld_sys_u32(&a.peer.pl->xseq);
@@ -701,7 +694,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             // particlesToGrid of the first Poisson step for a fresh population: local deposit, push, flags
             const unsigned e = xe + 1u;
             const int p = (int)(e & 1u);
-            int* mine = peer_grid(a.peer, a.peer.rank, p, a.peer.rank);
+            int* mine = a.grid[2];
             const int n = min(ld_volatile_i32(&st->n), a.capacity);
             const int rounded = (n + 31) & ~31;
             for (int i = (gwarp << 5) + c.lane; i < rounded; i += nwarp << 5) {
@@ -711,15 +704,21 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             }
             __syncthreads();
             if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
-                atomicMin(&st->bbox_lo[p][threadIdx.x], s_box[threadIdx.x]);
-                atomicMax(&st->bbox_hi[p][threadIdx.x], s_box[3 + threadIdx.x]);
+                atomicMin(&st->bbox_lo[2][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[2][threadIdx.x], s_box[3 + threadIdx.x]);
             }
-            grid_barrier(st, seq, []() {}, [&]() { fetch_after_b1(p); });
-            peer_push_rows(a.peer, p, bc.box_new, bc.box_pushed, gwarp, nwarp, c.lane, push_stage);
-            peer_push_drain(c.lane);
+            grid_barrier(st, seq, []() {}, [&]() { fetch_after_b1(2); fetch_step_start(xe); });
+            peer_add_rows(a.peer, p, a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
+            // the other summed grid still holds the last exchange of the PREVIOUS population: empty it before
+            // this rank's flag goes up, the peers add the exchange after this one into it
+            clear_box_rows(a.grid[xe & 1u], bc.box_old, gwarp, nwarp, c.lane);
+            peer_add_drain(c.lane);
             if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
-            grid_barrier(st, seq, [&]() { peer_commit(e); }, [&]() { fetch_step_start(e); }, true);
-            peer_sum(e);
+            grid_barrier(st, seq, [&]() {
+                for (int k = 0; k < 3; ++k) { v->bbox_lo[xe & 1u][k] = kGrid; v->bbox_hi[xe & 1u][k] = -1; }
+                peer_raise_flag(e);
+                peer_commit(e);
+            }, [&]() { fetch_step_start(e); }, true);
             xe = e;
         }
     }
@@ -731,15 +730,16 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         if (bc.hit_zero) break;                              // uniform: set before the previous barrier 3 released
         const int cur = bc.cur;
         // single GPU: three grids in rotation (gather / next deposit / being emptied).
-        // Peer mode: grid 0 holds the sum over the ranks of exchange xe; this rank deposits into its own
-        // grid of parity (xe+1)&1, pushes it to the peers, and the per-rank grids are added up after barrier 3.
-        const int nxt = kPeer ? (int)((xe + 1u) & 1u) : (cur + 1) % kRot;
+        // Peer mode: grid xe&1 holds the sum over the ranks of exchange xe and is gathered from; this rank
+        // deposits into its local grid 2, whose rows all ranks add into each other's grid (xe+1)&1 after barrier 1.
+        const int nxt = kPeer ? 2 : (cur + 1) % kRot;
         const int old = kPeer ? (int)(xe & 1u) : (cur + 2) % kRot;
-        f.A = kPeer ? a.grid[0] : a.grid[cur];                                              // gathered from (peer mode: the sum over the ranks)
-        f.B = kPeer ? peer_grid(a.peer, a.peer.rank, nxt, a.peer.rank) : a.grid[nxt];       // (local) deposit of the next step
-        int* const g_old = kPeer ? peer_grid(a.peer, a.peer.rank, old, a.peer.rank) : a.grid[old];
+        f.A = a.grid[kPeer ? old : cur];   // gathered from
+        f.B = a.grid[nxt];                 // (local) deposit of the next step
+        int* const g_old = a.grid[old];
         // g_old: single GPU: gathered from one step ago, emptied during this step's main phase;
-        //        peer mode: this rank's own deposit of exchange xe, emptied once this step's gathers are done
+        //        peer mode: the grid gathered from in THIS step, emptied once its gathers are done (barrier 1),
+        //        before this rank raises its flag -- the peers add the exchange after next into it
         c.g0 = (unsigned)bc.pidx * (unsigned)a.pt;
         const int n0 = min(bc.n, c.cap);
         const int chunks = (n0 + 31) >> 5;
@@ -808,23 +808,25 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // ---- every push of this step is done: list the holes and movers
         PIC_TRACE(3);          // barrier 1 passed
         if (kPeer) {
-            // every local deposit of this step is in place: hand this rank's box to the copy engine for its
-            // slot on every peer (asynchronous bulk stores over NVLink), and empty this rank's own grid of
-            // the previous exchange, which only this step's gathers still needed
-            peer_push_rows(a.peer, nxt, bc.box_new, bc.box_pushed, gwarp, nwarp, c.lane, push_stage);
+            // every local deposit of this step is in place: hand the rows of this rank's box to the copy engine,
+            // which adds them into the summed grid of every rank over NVLink (asynchronous bulk reduce-adds),
+            // and empty the grid this step gathered from
+            peer_add_rows(a.peer, (int)((xe + 1u) & 1u), a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             PIC_TRACE(11);
             clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
         }
         PIC_TRACE(8);
         const int scan_S = bc.S, scan_D = bc.D;              // (the scan's own __syncthreads separate these reads from the next fetch)
         compact_scan_body(c.s, st, scan_S, scan_D, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
+        // peer mode: the bulk adds were issued a whole scan ago; once they are complete this rank's flag goes
+        // up at barrier 2, a whole phase before anybody has to look at the flags (barrier 3)
+        if (kPeer) peer_add_drain(c.lane);
         PIC_TRACE(4);
-        grid_barrier(st, seq, []() {}, fetch_after_b2);
+        grid_barrier(st, seq, [&]() { if (kPeer) peer_raise_flag(xe + 1u); }, fetch_after_b2, kPeer);
         PIC_TRACE(5);
         compact_move_body(c.s, bc.H, a.holes, a.movers);
         if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
         if (threadIdx.x == 0) s_ticket = 0;
-        if (kPeer) peer_push_drain(c.lane);          // the pushes have had the whole compaction to cross NVLink
         PIC_TRACE(6);
         // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
         grid_barrier(st, seq, [&]() {
@@ -834,8 +836,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             else v->cur = nxt;
             v->ticket = 0;
             v->n_unfinished = 0;
-        }, [&]() { fetch_step_start(xe + 1u); }, kPeer);
-        if (kPeer) peer_sum(xe + 1u);
+        }, [&]() { fetch_step_start(xe + 1u); });
         ++xe;
         PIC_TRACE(7);
     }
