@@ -121,6 +121,8 @@ for _name, (_res, _args) in SIGNATURES.items():
 # not part of the public header: host copy of the bin-edge table, for the CPU-side exhaustive check
 lib.picb200_host_energy_edges.restype = None
 lib.picb200_host_energy_edges.argtypes = [_fp]
+lib.picb200_host_cell_bounds.restype = None
+lib.picb200_host_cell_bounds.argtypes = [_fp]
 
 
 class EngineError(RuntimeError):
@@ -362,6 +364,12 @@ def host_energy_edges():
     e = np.empty(TABLE_ROWS + 1, dtype=np.float32)
     lib.picb200_host_energy_edges(_ptr(e, _fp))
     return e
+
+
+def host_cell_bounds():
+    b = np.empty(GRID + 1, dtype=np.float32)
+    lib.picb200_host_cell_bounds(_ptr(b, _fp))
+    return b
 
 
 def pinned_empty(n, dtype):

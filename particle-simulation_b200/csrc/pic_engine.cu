@@ -576,7 +576,7 @@ int Sim::fused_steps(int steps) {
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
-                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0};
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, getenv("PICB200_DEBUG_SKIP_ADDS") ? 1 : 0};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
@@ -923,6 +923,8 @@ int picb200_load_table(const char* path, float* rows2) {
 }
 // host-side copy of the edge table, for the exhaustive CPU check of the device formula
 void picb200_host_energy_edges(float* out_edges) { build_energy_edges(out_edges); }
+// likewise the 513 cell-boundary coordinates cell_of_fast() probes
+void picb200_host_cell_bounds(float* out_bounds) { build_cell_bounds(out_bounds); }
 
 int picb200_peer_export(picb200_sim* sim, void* handle_out) { return sim->s.peer_export(handle_out); }
 int picb200_peer_connect(picb200_sim* sim, const void* handles) { return sim->s.peer_connect(handles); }

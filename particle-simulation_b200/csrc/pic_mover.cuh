@@ -348,6 +348,7 @@ struct FusedArgs {
     unsigned long long* trace;   // optional (PICB200_TRACE): 16 globaltimer stamps per block per Poisson step
     PeerArgs peer;               // kPeer only
     int initial_deposit;         // kPeer only: no summed grid holds this population yet
+    int debug_skip_adds;         // timing experiments only (PICB200_DEBUG_SKIP_ADDS): leave the bulk adds out (wrong fields!)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -811,7 +812,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             // every local deposit of this step is in place: hand the rows of this rank's box to the copy engine,
             // which adds them into the summed grid of every rank over NVLink (asynchronous bulk reduce-adds),
             // and empty the grid this step gathered from
-            peer_add_rows(a.peer, (int)((xe + 1u) & 1u), a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
+            if (!a.debug_skip_adds) peer_add_rows(a.peer, (int)((xe + 1u) & 1u), a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             PIC_TRACE(11);
             clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
         }

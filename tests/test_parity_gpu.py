@@ -264,6 +264,43 @@ def test_cfg2_full_size_invariants(engine):
         assert sim.charge_box(lo, hi).sum() == d.n               # deposition conserves the count
 
 
+def _state_digest(d):
+    """Order-independent digest of a population: per-electron 64-bit mix of id and the raw fp32 bits, summed."""
+    h = d.id.astype(np.uint64).copy()
+    for k in ("x", "y", "z", "vx", "vy", "vz"):
+        h = (h * np.uint64(0x9E3779B97F4A7C15)) ^ getattr(d, k).view(np.uint32).astype(np.uint64)
+    return int(h.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(h))
+
+
+def test_cfg2_full_size_all_schedulers_identical(engine):
+    """BASELINE cfg2 in all four scheduler modes: the schedulers differ in WHEN a child is pushed, never in
+    what happens to it, so counts and the multiset of (id, position, velocity) must be identical."""
+    ref = None
+    for mode in MODES:
+        with engine.Sim(mode=mode, init_n=1000000, poisson_steps=100, capacity=100000000, poisson_timestep=10) as sim:
+            sim.init_uniform(1000000)
+            sim.run_steps(100)
+            m = sim.summary()
+            got = (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) + _state_digest(sim.download())
+        if ref is None:
+            ref = got
+        assert got == ref, (mode, got, ref)
+
+
+def test_split_run_equals_single_run(engine):
+    """100 Poisson steps as 1 + 7 + 92 calls == one call (the persistent kernel carries no hidden state
+    from launch to launch; RNG counters depend on the global step only)."""
+    digests = []
+    for parts in ((100,), (1, 7, 92)):
+        with engine.Sim(mode=0, init_n=300000, poisson_steps=100, capacity=3000000, poisson_timestep=10) as sim:
+            sim.init_uniform(300000)
+            for k in parts:
+                sim.run_steps(k)
+            m = sim.summary()
+            digests.append((m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) + _state_digest(sim.download()))
+    assert digests[0] == digests[1] and digests[0][1] > 1000
+
+
 # ------------------------------------------------------------------------------------------
 # the outer boundary: the `run` CLI and its stdout contract
 # ------------------------------------------------------------------------------------------
