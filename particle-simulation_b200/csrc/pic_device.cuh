@@ -51,12 +51,21 @@ struct DevState {
     int last_n_after_mobility;
     int ticket;             // (spare work counter)
     long long total_added, total_removed;
+    // -- lazy compaction inside the fused kernel (always back to hw == n when a launch ends)
+    int hw;                 // slots in use: [0,hw) holds the n live electrons and hw-n dead ones
+    int do_compact;         // this Poisson step ends with remove_dead_particles (else the holes stay)
+    int scan_S, scan_D;     // its arguments: slots to look at, dead ones among them
+    int parked;             // children of this step waiting for the compaction to make room (see FusedArgs::park)
+    int error;              // 2: more children parked than the parking area holds, 3: a spilled child found no slot
     // -- hot atomics, one 128-byte line each so they do not serialise behind one another in L2
-    alignas(128) int n_alloc;                   // append cursor during the mobility phase (may overshoot capacity)
+    alignas(128) int n_alloc;                   // the reference's counter n during the mobility phase (may overshoot capacity)
+    int top_alloc;                              // fused kernel: slots taken above the high-water mark; the two form ONE 64-bit
+                                                // word so that a batch of children draws from both with a single atomic
     alignas(128) int n_dead;                    // electrons marked DEAD in this Poisson step
     alignas(128) unsigned long long pushes;     // updateParticle evaluations
     alignas(128) unsigned bar_count;            // grid barrier: arrivals
     alignas(128) unsigned bar_release;          // grid barrier: releases
+    alignas(128) int n_parked;                  // parking cursor
     alignas(128) int pad_;
 };
 
@@ -246,7 +255,7 @@ __device__ __forceinline__ void clear_box_body(const DevState* st, int* __restri
     }
 }
 __global__ void k_clear_box(const DevState* st, int* __restrict__ charge, int which) { clear_box_body(st, charge, which); }
-__global__ void k_set_n(DevState* st, int n) { st->n = n; st->n_alloc = n; }
+__global__ void k_set_n(DevState* st, int n) { st->n = n; st->n_alloc = n; st->top_alloc = n; }
 // which: 0 .. kGrids-1 = that grid's box, kGrids = all
 __global__ void k_reset_bbox(DevState* st, int which) {
     if (threadIdx.x < 3)
@@ -372,6 +381,7 @@ __global__ void k_compact_move(Soa s, const DevState* st, const int* __restrict_
 // Bookkeeping the reference does on the host after each phase (src/pic.cu:539-559), on the device.
 __global__ void k_mobility_begin(DevState* st) {
     st->n_alloc = st->n;
+    st->top_alloc = st->n;
     st->n_dead = 0;
     st->n_holes = 0; st->n_movers = 0;
     st->bar_count = 0; st->bar_release = 0;
@@ -393,6 +403,49 @@ __device__ __forceinline__ void step_end_body(DevState* st_, int capacity, StepL
     st->n = L;
     st->n_alloc = L;
     st->n_dead = 0; st->n_holes = 0; st->n_movers = 0;
+    // src/pic.cu:556-559; with several ranks an empty slab keeps stepping (the collective needs it)
+    if (L == 0 && stop_at_zero) st->hit_zero = 1;
+    st->poisson_index = p + 1;
+}
+// The same bookkeeping inside the fused kernel, which does NOT compact after every Poisson step: a child
+// moves into a slot whose electron has died (every warp keeps the free slots it comes across), and what
+// holes remain stay where they are -- the chunks skip them -- until they are worth a compaction.  `n`, the
+// totals and the overflow rule are the reference's: a child exists iff the reference's counter n (n_alloc,
+// which starts every step at the number of LIVE electrons) is below capacity when it is born; only the slot
+// it lands in differs (a free one, else the next above the high-water mark, top_alloc).  Should the slots
+// above the mark run out while the reference's counter has not reached the capacity, the finished child is
+// parked and placed by the compaction this step then ends with.  Publishes do_compact, scan_S, scan_D,
+// parked, hw.
+__device__ __forceinline__ void step_end_fused(DevState* st_, int capacity, StepLog* log, int log_len, int stop_at_zero, int hw_start,
+                                               bool last_step, int policy /* 0 lazy, 1 every step, 2 lazy without the capacity guard (tests) */) {
+    volatile DevState* st = st_;
+    const int n0 = st->n;
+    const int after = st->n_alloc;                 // may overshoot capacity, like the reference's n
+    const int S = min(after, capacity);
+    const int L = S - st->n_dead;
+    const int parked = min(st->n_parked, capacity);
+    st->total_added = st->total_added + (long long)(after - n0);    // src/pic.cu:540
+    st->total_removed = st->total_removed + (long long)(after - L); // src/pic.cu:552
+    st->last_n_after_mobility = after;
+    if (after >= capacity) st->overflow_steps = st->overflow_steps + 1;   // src/pic.cu:544
+    const int p = st->poisson_index;
+    if (log && p < log_len) { log[p].n_after_mobility = after; log[p].n_after_compaction = L; }
+    const int top = st->top_alloc;                 // may overshoot, too
+    st->n = L;
+    st->n_alloc = L;
+    st->n_dead = 0; st->n_holes = 0; st->n_movers = 0; st->n_parked = 0;
+    int hw = max(min(top, capacity), hw_start);
+    const int holes = hw - (L - parked);
+    const long long births = (long long)S - n0;
+    // compact when the launch ends (the host sees slots [0,n) alive), when children wait for room, when
+    // more than one slot in eight is dead, or when the next step could run into the capacity
+    bool compact = last_step || policy == 1 || parked > 0 || holes > (L >> 3) || (policy != 2 && (long long)hw + 2 * births > (long long)capacity);
+    if (holes == 0) compact = false;
+    if (L == 0) { compact = false; hw = 0; }       // nobody left: nothing to move
+    st->do_compact = compact ? 1 : 0;
+    st->scan_S = hw; st->scan_D = holes; st->parked = compact ? parked : 0;
+    st->hw = compact ? L : hw;
+    st->top_alloc = compact ? L : hw;
     // src/pic.cu:556-559; with several ranks an empty slab keeps stepping (the collective needs it)
     if (L == 0 && stop_at_zero) st->hit_zero = 1;
     st->poisson_index = p + 1;

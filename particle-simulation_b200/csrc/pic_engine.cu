@@ -93,6 +93,10 @@ struct Sim {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     Soa soa{};
+    Soa park{};             // parking area of the fused kernel's lazy compaction (step_end_fused)
+    void* park_base = nullptr;
+    int park_cap = 0;
+    int compact_policy = 0;
     void* soa_base = nullptr;
     int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
@@ -200,6 +204,7 @@ void Sim::release() {
     cudaFree(pl); pl = nullptr;
     if (h_pl) { cudaFreeHost(h_pl); h_pl = nullptr; }
     cudaFree(soa_base); soa_base = nullptr;
+    cudaFree(park_base); park_base = nullptr;
     for (int g = 0; g < kGrids; ++g) { cudaFree(grid[g]); grid[g] = nullptr; }
     cudaFree(holes); holes = nullptr;
     cudaFree(movers); movers = nullptr;
@@ -272,6 +277,20 @@ int Sim::create(const picb200_config* c) {
     soa.ts = reinterpret_cast<int*>(p); p += f_bytes;
     soa.id = reinterpret_cast<unsigned long long*>(p);
     CK(cudaMemsetAsync(soa.ts, 0, f_bytes, stream), "Electron alloc");
+    {
+        park_cap = (int)std::min<size_t>(cap, (size_t)1 << 20);
+        const size_t pf = align_up((size_t)park_cap * 4, 256), pi = align_up((size_t)park_cap * 8, 256);
+        CK(cudaMalloc(&park_base, pf * 10 + pi), "Electron alloc");
+        unsigned char* q = static_cast<unsigned char*>(park_base);
+        float** pfields[9] = {&park.x, &park.y, &park.z, &park.vx, &park.vy, &park.vz, &park.ax, &park.ay, &park.az};
+        for (auto f : pfields) { *f = reinterpret_cast<float*>(q); q += pf; }
+        park.ts = reinterpret_cast<int*>(q); q += pf;
+        park.id = reinterpret_cast<unsigned long long*>(q);
+        // PICB200_COMPACT=eager: remove_dead_particles after every Poisson step, as the reference does;
+        // =noguard: lazy without the capacity guard (exercises the parking path in the tests)
+        const char* pol = getenv("PICB200_COMPACT");
+        compact_policy = !pol ? 0 : (!strcmp(pol, "eager") ? 1 : (!strcmp(pol, "noguard") ? 2 : 0));
+    }
 
     // ---- compaction work lists: at most min(D, S-D) <= cap/2 entries each
     list_cap = cap / 2 + 1;
@@ -394,6 +413,8 @@ int Sim::sync_state() {
     CK(cudaStreamSynchronize(stream), "State readback");
     cur = h_st->cur;
     if (pl && h_pl->error) return fail("a peer rank did not reach the charge exchange within 20 s", "Charge exchange");
+    if (h_st->error == 2) return fail("more children waited for a compaction than the parking area holds", "Mobility phase");
+    if (h_st->error == 3) return fail("a spilled child found no slot below the capacity", "Mobility phase");
     return collect_spans();
 }
 
@@ -576,7 +597,7 @@ int Sim::fused_steps(int steps) {
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
-                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, getenv("PICB200_DEBUG_SKIP_ADDS") ? 1 : 0};
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, compact_policy};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");

@@ -45,6 +45,7 @@ struct MoverCtx {
     const float* edge;
     uint32_t* stage;
     int cap, pt, lane, stepwise;
+    int* pool;           // fused kernel: free slots this warp has come across in the current Poisson step (shared memory)
     unsigned g0;
     uint2 seed;
 };
@@ -55,6 +56,19 @@ __device__ __forceinline__ int reserve_slots(const MoverCtx& c, int count) {
     int base = 0;
     if (c.lane == 0) base = (ld_volatile_i32(&c.st->n_alloc) < c.cap) ? atomicAdd(&c.st->n_alloc, count) : c.cap;
     return __shfl_sync(kFull, base, 0);
+}
+
+// Fused kernel: `count` children are born, `from_top` of them need a slot above the high-water mark (the
+// others move into free slots the warp holds).  ONE 64-bit atomic advances the reference's counter n (low
+// word: decides which children exist, src/pic.cu:222) and the mark (high word).
+constexpr int kPoolSlots = 64;
+__device__ __forceinline__ void reserve_fused(const MoverCtx& c, int count, int from_top, int& vbase, int& tbase) {
+    unsigned long long old = (unsigned long long)(unsigned)c.cap;           // exhausted: nobody is born
+    if (c.lane == 0 && ld_volatile_i32(&c.st->n_alloc) < c.cap)
+        old = atomicAdd(reinterpret_cast<unsigned long long*>(&c.st->n_alloc), (unsigned long long)(unsigned)count | ((unsigned long long)(unsigned)from_top << 32));
+    old = __shfl_sync(kFull, old, 0);
+    vbase = (int)(unsigned)(old & 0xffffffffull);
+    tbase = (int)(unsigned)(old >> 32);
 }
 
 // A stage entry carries the parent's id and the birth step; the child's own id is derived when the
@@ -69,8 +83,15 @@ __device__ __forceinline__ unsigned long long staged_child_id(const MoverCtx& c,
 template <bool kCount>
 __device__ __forceinline__ void stage_spill(const MoverCtx& c, int count) {
     __syncwarp();
-    const int slot = reserve_slots(c, count) + c.lane;
-    const bool w = c.lane < count && slot < c.cap;
+    int vslot, slot;
+    if (c.pool) {            // fused kernel: the reference's index decides whether the child exists, it lives above the mark
+        reserve_fused(c, count, count, vslot, slot);
+        vslot += c.lane; slot += c.lane;
+        if (c.lane < count && vslot < c.cap && slot >= c.cap) *(volatile int*)&c.st->error = 3;   // unfinished children cannot be parked
+    } else {
+        vslot = slot = reserve_slots(c, count) + c.lane;
+    }
+    const bool w = c.lane < count && vslot < c.cap && slot < c.cap;
     if (w) {
         const uint32_t* g = c.stage + c.lane;
         __stcg(c.s.x + slot, __uint_as_float(g[0 * 32])); __stcg(c.s.y + slot, __uint_as_float(g[1 * 32])); __stcg(c.s.z + slot, __uint_as_float(g[2 * 32]));
@@ -264,6 +285,7 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     c.pt = a.pt;
     c.lane = threadIdx.x & 31;
     c.stepwise = a.stepwise;
+    c.pool = nullptr;
     c.g0 = (unsigned)a.st->poisson_index * (unsigned)a.pt;
     c.seed = a.seed;
 
@@ -348,7 +370,9 @@ struct FusedArgs {
     unsigned long long* trace;   // optional (PICB200_TRACE): 16 globaltimer stamps per block per Poisson step
     PeerArgs peer;               // kPeer only
     int initial_deposit;         // kPeer only: no summed grid holds this population yet
-    int debug_skip_adds;         // timing experiments only (PICB200_DEBUG_SKIP_ADDS): leave the bulk adds out (wrong fields!)
+    Soa park;                    // parking area for step_end_fused's rare case (park_cap electrons)
+    int park_cap;
+    int compact_policy;          // 0: lazy (default); 1: after every Poisson step (PICB200_COMPACT=eager); 2: lazy, no capacity guard (tests)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -425,7 +449,9 @@ __device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F acti
 // What one thread per block reads from the control block after a grid barrier, for the whole block.
 struct BlockBc {
     int hit_zero, cur, pidx, n;     // start of a Poisson step
+    int hw;                         // slots in use (>= n: holes of earlier steps stay in place until a compaction)
     int gen_hi, S, D;               // after barrier 1
+    int do_compact, parked;         // after the LAST barrier 1 of a step: does it end with a compaction?
     int H;                          // after barrier 2
     int box_old[6];                 // box of the grid this step empties (lo xyz, hi xyz)
     int box_new[6];                 // peer mode: box of this step's own (local) deposit
@@ -438,6 +464,8 @@ struct FusedCtx {
     int* s_box;
     double efc;
     bool store_acc;   // last Poisson step of this launch: the frozen acceleration becomes visible to the host
+    Soa park;         // finished children whose shifted slot passed the capacity (step_end_fused)
+    int park_cap;
 };
 
 
@@ -495,7 +523,7 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
 // mobility step t, so the step loop is straight-line code: the Philox block changes for the whole
 // warp at once, dead lanes keep computing values nobody stores instead of branching around the body,
 // and the only branch is the warp vote "somebody spawned".
-__device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead) {
+__device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead, int& npool) {
     const int i = i0 + c.lane;
     const bool in = i < end;
     float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f;
@@ -507,21 +535,22 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
         ts = __ldcg(c.s.ts + i);
         id = __ldcg(c.s.id + i);
     }
-    if (__any_sync(kFull, ts != -1)) {          // uploaded populations may carry other timestamps
+    if (__any_sync(kFull, (ts != -1) & (ts != kDead))) {      // uploaded populations may carry other timestamps
         fused_chunk<false>(c, f, i0, end, staged, pushes, dead);
         return;
     }
+    const bool was_alive = in & (ts != kDead);                // holes of earlier Poisson steps stay in place (lazy compaction)
     // updateGrid + gridToParticles for this electron's own cell (src/grid_operations.cu:29-72)
     float ax = 0.f, ay = 0.f, az = 0.f;
     const float x0 = x, y0 = y, z0 = z;
     int ix = cell_of_fast(x, f.bnd), iy = cell_of_fast(y, f.bnd), iz = cell_of_fast(z, f.bnd);
-    if (in) {
+    if (was_alive) {
         gather_field(f, ix, iy, iz, ax, ay, az);
         if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
     }
     const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
     const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
-    bool alive = in;
+    bool alive = was_alive;
     unsigned g = c.g0;
     uint4 rnd = make_uint4(0, 0, 0, 0);
 #pragma unroll 1
@@ -565,12 +594,22 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
         dead += die ? 1 : 0;
         alive = alive & !die;
     }
-    if (in) {
+    if (was_alive) {
         if (alive) {
             __stcg(c.s.x + i, x); __stcg(c.s.y + i, y); __stcg(c.s.z + i, z);
             __stcg(c.s.vx + i, vx); __stcg(c.s.vy + i, vy); __stcg(c.s.vz + i, vz);
         } else {
             __stcg(c.s.ts + i, kDead);
+        }
+    }
+    // slots of this chunk whose electron arrived dead or died just now: this warp's children move in (fused_staged)
+    {
+        const bool free_slot = in & !alive;
+        const unsigned fm = __ballot_sync(kFull, free_slot);
+        if (fm) {
+            const int r = npool + __popc(fm & lanemask_lt());
+            if (free_slot && r < kPoolSlots) c.pool[r] = i;
+            npool = min(kPoolSlots, npool + __popc(fm));
         }
     }
     // particlesToGrid of the next Poisson step; the cell is recomputed only where the coordinate changed
@@ -581,7 +620,7 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
 }
 
 // children out of the warp's stage: push, deposit, store once (see process_staged)
-__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead) {
+__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead, int& npool) {
     const int k = staged;
     __syncwarp();
     El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -596,11 +635,37 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
     }
     staged = 0;
     __syncwarp();
-    const int slot = reserve_slots(c, k) + c.lane;
-    const bool in = c.lane < k && slot < c.cap;
-    bool alive = in;
+    // the first p children move into free slots this warp holds, the others go above the high-water mark
+    const int p = min(k, npool);
+    int vslot, tbase;
+    reserve_fused(c, k, k - p, vslot, tbase);
+    vslot += c.lane;                                         // the reference's index (src/pic.cu:222): the child exists iff it is < capacity
+    const int slot = c.lane < p ? c.pool[npool - 1 - c.lane] : tbase + (c.lane - p);
+    npool -= p;
+    __syncwarp();                                            // pool entries read before anybody adds new ones
+    const bool born = c.lane < k && vslot < c.cap;
+    const bool in = born && slot < c.cap;
+    bool alive = born;
     bool touched = false;
     advance<true>(c, e, alive, tb + 1, c.pt, staged, pushes, dead, touched);
+    if (__any_sync(kFull, born & !in)) {                     // rare: no room above the holes -> parked until this step's compaction
+        const bool park = born && !in && alive;
+        const unsigned pm = __ballot_sync(kFull, park);
+        int pb = 0;
+        if (c.lane == 0 && pm) pb = atomicAdd(&c.st->n_parked, __popc(pm));
+        pb = __shfl_sync(kFull, pb, 0) + __popc(pm & lanemask_lt());
+        if (park) {
+            if (pb < f.park_cap) {
+                const Soa& q = f.park;
+                __stcg(q.x + pb, e.x); __stcg(q.y + pb, e.y); __stcg(q.z + pb, e.z);
+                __stcg(q.vx + pb, e.vx); __stcg(q.vy + pb, e.vy); __stcg(q.vz + pb, e.vz);
+                __stcg(q.ax + pb, e.ax); __stcg(q.ay + pb, e.ay); __stcg(q.az + pb, e.az);
+                __stcg(q.id + pb, e.id);
+            } else {
+                *(volatile int*)&c.st->error = 2;
+            }
+        }
+    }
     if (in) {
         __stcg(c.s.x + slot, e.x); __stcg(c.s.y + slot, e.y); __stcg(c.s.z + slot, e.z);
         __stcg(c.s.vx + slot, e.vx); __stcg(c.s.vy + slot, e.vy); __stcg(c.s.vz + slot, e.vz);
@@ -613,7 +678,7 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
 
 constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
-constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPushStageBytesPerWarp); }
+constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPushStageBytesPerWarp + kPoolSlots * 4); }
 
 template <bool kPeer>
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
@@ -648,11 +713,14 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
     f.s_box = s_box;
     f.efc = a.efc;
+    f.park = a.park;
+    f.park_cap = a.park_cap;
 
     unsigned seq = 0;
     const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
     unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
     int* const push_stage = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPushSegCells;
+    c.pool = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * (kStageBytesPerWarp + kPushStageBytesPerWarp)) + (threadIdx.x >> 5) * kPoolSlots;
     volatile DevState* const v = st;
 
     // ---- what ONE thread per block fetches after each grid barrier (BlockBc): every thread asking L2 for
@@ -660,13 +728,20 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     auto load_box = [&](int* dst, const volatile int* lo, const volatile int* hi) {
         for (int k = 0; k < 3; ++k) { dst[k] = lo[k]; dst[3 + k] = hi[k]; }
     };
+    bool launch_start = true;                                // every launch starts compacted: hw == n
     auto fetch_step_start = [&](unsigned e_done) {           // e_done: exchanges complete (peer mode)
         bc.hit_zero = v->hit_zero; bc.cur = v->cur; bc.pidx = v->poisson_index; bc.n = v->n;
+        bc.hw = launch_start ? bc.n : v->hw;
+        s_ticket = 0;
+        for (int k = 0; k < 6; ++k) s_box[k] = k < 3 ? kGrid : -1;
         const int old = kPeer ? (int)(e_done & 1u) : (bc.cur + 2) % kRot;
         load_box(bc.box_old, v->bbox_lo[old], v->bbox_hi[old]);
     };
     auto fetch_after_b1 = [&](int nxt) {
-        bc.gen_hi = v->gen_hi; bc.S = min(v->n_alloc, a.capacity); bc.D = v->n_dead;
+        bc.gen_hi = v->gen_hi;
+        for (int k = 0; k < 6; ++k) s_box[k] = k < 3 ? kGrid : -1;       // merged into the global box before the barrier
+        if (bc.gen_hi >= 0) return;                                     // a fall-back pass comes first
+        bc.S = v->scan_S; bc.D = v->scan_D; bc.do_compact = v->do_compact; bc.parked = v->parked;
         if (kPeer) load_box(bc.box_new, v->bbox_lo[nxt], v->bbox_hi[nxt]);
     };
     auto fetch_after_b2 = [&]() { bc.H = min(v->n_holes, v->n_movers); };
@@ -708,7 +783,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 atomicMin(&st->bbox_lo[2][threadIdx.x], s_box[threadIdx.x]);
                 atomicMax(&st->bbox_hi[2][threadIdx.x], s_box[3 + threadIdx.x]);
             }
-            grid_barrier(st, seq, []() {}, [&]() { fetch_after_b1(2); fetch_step_start(xe); });
+            grid_barrier(st, seq, []() {}, [&]() { load_box(bc.box_new, v->bbox_lo[2], v->bbox_hi[2]); fetch_step_start(xe); });
             peer_add_rows(a.peer, p, a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             // the other summed grid still holds the last exchange of the PREVIOUS population: empty it before
             // this rank's flag goes up, the peers add the exchange after this one into it
@@ -728,7 +803,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         __syncthreads();
     }
     for (int step = 0; step < a.steps; ++step) {
-        if (bc.hit_zero) break;                              // uniform: set before the previous barrier 3 released
+        if (bc.hit_zero) break;                              // uniform: set before the previous step's last barrier released
+        launch_start = false;
         const int cur = bc.cur;
         // single GPU: three grids in rotation (gather / next deposit / being emptied).
         // Peer mode: grid xe&1 holds the sum over the ranks of exchange xe and is gathered from; this rank
@@ -742,9 +818,11 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         //        peer mode: the grid gathered from in THIS step, emptied once its gathers are done (barrier 1),
         //        before this rank raises its flag -- the peers add the exchange after next into it
         c.g0 = (unsigned)bc.pidx * (unsigned)a.pt;
-        const int n0 = min(bc.n, c.cap);
-        const int chunks = (n0 + 31) >> 5;
+        const int hw0 = min(bc.hw, c.cap);                   // slots in use: bc.n live electrons and hw0 - n holes
+        const int chunks = (hw0 + 31) >> 5;
+        const bool last_step = step == a.steps - 1;
         int staged = 0;
+        int npool = 0;                                       // free slots this warp holds (valid within this Poisson step only)
         unsigned pushes = 0;
         int dead = 0;
         PIC_TRACE(0);
@@ -752,23 +830,25 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // ---- generation 0 (+ this warp's own children): chunk k of block b is global chunk k*gridDim+b,
         // so every SM gets the same number of chunks to within one; inside the block the warps draw
         // their next chunk from a shared-memory ticket, which evens out the children they pick up
-        f.store_acc = step == a.steps - 1;
+        f.store_acc = last_step;
         for (;;) {
             int k = 0;
             if (c.lane == 0) k = atomicAdd(&s_ticket, 1);
             const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
             if (chunk >= chunks) break;
-            fused_chunk_fast(c, f, chunk << 5, n0, staged, pushes, dead);
-            if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
+            fused_chunk_fast(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
+            if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead, npool);
         }
-        while (staged) fused_staged(c, f, staged, pushes, dead);
+        while (staged) fused_staged(c, f, staged, pushes, dead, npool);
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
         if (!kPeer) clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
         PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
-        // ---- barrier 1 (+ fall-back passes over spilled children)
-        int lo = n0;
+        // ---- barrier 1 (+ fall-back passes over spilled children).  The last block to arrive at the LAST
+        // barrier 1 of the step does the host's bookkeeping of src/pic.cu:539-559 and decides whether this
+        // step ends with remove_dead_particles or leaves its holes in place (step_end_fused)
+        int lo = hw0;
         for (;;) {
             for (int o = 16; o > 0; o >>= 1) {
                 pushes += __shfl_down_sync(kFull, pushes, o);
@@ -793,51 +873,84 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             grid_barrier(st, seq, [&]() {
                 const int unfinished = v->n_unfinished;
                 v->n_unfinished = 0;
-                v->gen_hi = unfinished > 0 ? min(v->n_alloc, c.cap) : -1;
-            }, [&]() { fetch_after_b1(nxt); });
+                if (unfinished > 0) {
+                    v->gen_hi = min(v->top_alloc, c.cap);
+                    return;
+                }
+                v->gen_hi = -1;
+                step_end_fused(st, c.cap, a.log, a.log_len, a.stop_at_zero, hw0, last_step, a.compact_policy);
+                if (!kPeer) {                                    // the grids change roles; the emptied one has no box
+                    for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
+                    v->cur = nxt;
+                }
+            }, [&]() {
+                fetch_after_b1(nxt);
+                if (!kPeer && bc.gen_hi < 0 && !bc.do_compact) fetch_step_start(0u);     // straight on to the next Poisson step
+            });
             const int hi = bc.gen_hi;
             if (hi < 0) break;
             const int rounded = (hi - lo + 31) & ~31;
             for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x) {
                 fused_chunk<true>(c, f, lo + k, hi, staged, pushes, dead);
-                if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead);
+                if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead, npool);
             }
-            while (staged) fused_staged(c, f, staged, pushes, dead);
+            while (staged) fused_staged(c, f, staged, pushes, dead, npool);
             lo = hi;
         }
+        PIC_TRACE(3);          // barrier 1 passed: every push of this step is done
+        const bool compact = bc.do_compact != 0;             // uniform over the grid
+        if (!kPeer && !compact) { PIC_TRACE(7); continue; }
 
-        // ---- every push of this step is done: list the holes and movers
-        PIC_TRACE(3);          // barrier 1 passed
         if (kPeer) {
             // every local deposit of this step is in place: hand the rows of this rank's box to the copy engine,
             // which adds them into the summed grid of every rank over NVLink (asynchronous bulk reduce-adds),
             // and empty the grid this step gathered from
-            if (!a.debug_skip_adds) peer_add_rows(a.peer, (int)((xe + 1u) & 1u), a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
+            peer_add_rows(a.peer, (int)((xe + 1u) & 1u), a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             PIC_TRACE(11);
             clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
         }
         PIC_TRACE(8);
-        const int scan_S = bc.S, scan_D = bc.D;              // (the scan's own __syncthreads separate these reads from the next fetch)
-        compact_scan_body(c.s, st, scan_S, scan_D, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
-        // peer mode: the bulk adds were issued a whole scan ago; once they are complete this rank's flag goes
-        // up at barrier 2, a whole phase before anybody has to look at the flags (barrier 3)
+        // ---- remove_dead_particles (src/pic.cu:320-357), when this step has one: list the holes below the
+        // new n and the live electrons above it
+        if (compact) compact_scan_body(c.s, st, bc.S, bc.D, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
+        // peer mode: the bulk adds were issued a whole scan ago; once they are complete this rank's flag goes up
         if (kPeer) peer_add_drain(c.lane);
         PIC_TRACE(4);
-        grid_barrier(st, seq, [&]() { if (kPeer) peer_raise_flag(xe + 1u); }, fetch_after_b2, kPeer);
-        PIC_TRACE(5);
-        compact_move_body(c.s, bc.H, a.holes, a.movers);
-        if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
-        if (threadIdx.x == 0) s_ticket = 0;
-        PIC_TRACE(6);
-        // ---- barrier 3: bookkeeping of src/pic.cu:539-559 by the last block; grids swap roles
         grid_barrier(st, seq, [&]() {
-            step_end_body(st, c.cap, a.log, a.log_len, a.stop_at_zero);
-            for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
-            if (kPeer) peer_commit(xe + 1u);
-            else v->cur = nxt;
-            v->ticket = 0;
-            v->n_unfinished = 0;
-        }, [&]() { fetch_step_start(xe + 1u); });
+            if (kPeer) {
+                for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
+                peer_raise_flag(xe + 1u);
+                if (!compact) peer_commit(xe + 1u);              // nothing left to hide the wait behind
+            }
+        }, [&]() {
+            if (compact) fetch_after_b2();
+            else fetch_step_start(xe + 1u);
+        }, kPeer);
+        PIC_TRACE(5);
+        if (compact) {
+            compact_move_body(c.s, bc.H, a.holes, a.movers);
+            PIC_TRACE(6);
+            const int parked = bc.parked;
+            if (parked > 0) {
+                // children that found no room above the holes: the compaction has made it (slots n - parked .. n)
+                grid_barrier(st, seq, []() {});
+                const int n_new = min(v->n, c.cap) - parked;
+                for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < parked; k += gridDim.x * blockDim.x) {
+                    const Soa& q = a.park;
+                    const int dst = n_new + k;
+                    __stcg(c.s.x + dst, __ldcg(q.x + k)); __stcg(c.s.y + dst, __ldcg(q.y + k)); __stcg(c.s.z + dst, __ldcg(q.z + k));
+                    __stcg(c.s.vx + dst, __ldcg(q.vx + k)); __stcg(c.s.vy + dst, __ldcg(q.vy + k)); __stcg(c.s.vz + dst, __ldcg(q.vz + k));
+                    __stcg(c.s.ax + dst, __ldcg(q.ax + k)); __stcg(c.s.ay + dst, __ldcg(q.ay + k)); __stcg(c.s.az + dst, __ldcg(q.az + k));
+                    __stcg(c.s.ts + dst, -1);
+                    __stcg(c.s.id + dst, __ldcg(q.id + k));
+                }
+            }
+            // ---- barrier 3: the store is dense again
+            grid_barrier(st, seq, [&]() {
+                v->n_holes = 0; v->n_movers = 0;
+                if (kPeer) peer_commit(xe + 1u);
+            }, [&]() { fetch_step_start(xe + 1u); });
+        }
         ++xe;
         PIC_TRACE(7);
     }
