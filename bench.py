@@ -260,7 +260,7 @@ def run_ours(args):
         "phases_ms_per_step": {k: v for k, v in phases.items() if k.endswith("_ms")},
         "clocks": clocks,
     }
-    if world == 1:
+    if world == 1 and not os.environ.get("PICB200_BENCH_NO_CPU"):      # (tools/ab.sh: kernel A/B runs skip the 12 s CPU leg)
         try:
             line["cpu_baseline"] = cpu_baseline()
         except Exception as e:  # the bench line must still be printed
