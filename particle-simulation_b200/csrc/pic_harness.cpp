@@ -17,7 +17,10 @@ static const char* kSchedulerName[] = {"Dynamic", "CPU Sync", "Naive", "Dynamic 
 int picb200_harness_run(const picb200_config* cfg_in, int gpus) {
     if (gpus <= 1) {
         picb200_summary sum;
-        return picb200_run(cfg_in, &sum, nullptr, 0);
+        const int rc = picb200_run(cfg_in, &sum, nullptr, 0);
+        // PICB200_PRINT_PUSHES=1: the push count, on stderr (stdout keeps the reference's lines only)
+        if (!rc && getenv("PICB200_PRINT_PUSHES")) fprintf(stderr, "pushes %lld\n", (long long)sum.pushes);
+        return rc;
     }
     // Particle slabs: rank r owns initial ids [r*n/k, (r+1)*n/k) and capacity max_n/k.
     picb200_config base = *cfg_in;
@@ -108,6 +111,7 @@ int picb200_harness_run(const picb200_config* cfg_in, int gpus) {
     printf("Particles added: %lld\n", (long long)tot.total_added);
     printf("Particles removed: %lld\n", (long long)tot.total_removed);
     printf("GPU time of program: %f ms\n", tot.gpu_ms);
+    if (getenv("PICB200_PRINT_PUSHES")) fprintf(stderr, "pushes %lld\n", (long long)tot.pushes);
     return 0;
 }
 
