@@ -124,6 +124,22 @@ def all_sum(dist, v):
     return float(t.item())
 
 
+def ncu_traffic(pushes_per_launch):
+    """DRAM bytes of one k_poisson_fused launch of this bench: dram__bytes_read.sum + dram__bytes_write.sum of the committed
+    `ncu --set full` capture (profiles/*_ncu_traffic.json, written by tools/refresh_profiles.sh), scaled from the captured
+    launch's push count to this launch's (the capture runs 10 Poisson steps of the same population, the bench 100)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_traffic.json")))
+    if not files:
+        return None, "no ncu capture committed"
+    t = json.load(open(files[-1]))
+    if not t.get("pushes_in_launch"):
+        return None, f"{os.path.basename(files[-1])}: push count of the captured launch missing"
+    per_push = (t["dram_bytes_read"] + t["dram_bytes_write"]) / t["pushes_in_launch"]
+    return per_push * pushes_per_launch, (f"{os.path.basename(files[-1])} (commit {t['commit']}): {per_push:.2f} B of DRAM traffic per push in the captured launch "
+                                          f"x {pushes_per_launch:.4g} pushes per launch here; bytes")
+
+
 def cpu_baseline(budget_s=12.0):
     """The CPU port (oracle/, OpenMP over all host cores) on a bounded sample of cfg2: its first
     Poisson steps until ~budget_s of wall time is used."""
@@ -243,6 +259,7 @@ def run_ours(args):
     peak, peak_src = measured_hbm_peak()
     mover_s = prof["mover_ms"] / 1e3
     achieved = pushes * BYTES_PER_PUSH / mover_s / 1e9 if mover_s > 0 else None
+    traffic, traffic_note = ncu_traffic(pushes / max(1, int(prof["mover_launches"])))
     line = {
         "metric": METRIC, "value": pushes_all / t_max, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_max * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -253,7 +270,7 @@ def run_ours(args):
         "e2e": {"value": e2e_pushes_all / e2e_max, "unit": UNIT, "h2d_bytes_per_step": n_local * 48, "d2h_bytes_per_step": d2h_bytes // max(1, args.steps),
                 "what": "picb200_upload (pinned host SoA) + picb200_run_steps + picb200_download (pinned host SoA), wall clock"},
         "gpu_launches": int(prof["launches"]),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_note": traffic_note,
                      "kernel": "k_poisson_fused", "launches": int(prof["mover_launches"]), "kernel_ms_total": prof["mover_ms"],
                      "kernel_share_of_step": prof["mover_ms"] / gpu_ms if gpu_ms else None,
                      "accounting": f"{BYTES_PER_PUSH:.0f} B per push x pushes per launch (SURVEY.md 8d); peak = {peak_src}; electrons stay in registers for all 10 mobility steps of a launch, so required HBM traffic is ~7.6 B/push and the 68-B-accounted figure may exceed the peak"},

@@ -15,7 +15,9 @@ with eng.Sim(mode=mode, init_n=n, poisson_steps=P + warm, capacity=cap, poisson_
     sim.init_uniform(n)
     if warm:
         sim.run_steps(warm)
+    before = sim.summary()["pushes"]
     sim.set_profiling(2)
     sim.run_steps(P)
+    print("pushes_in_profiled_launch", sim.summary()["pushes"] - before)
     print(sim.summary())
     print(sim.profile())
