@@ -482,6 +482,66 @@ __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, 
 }
 
 // generation-0 chunk of the fused kernel: gather from A, push, deposit into B
+// One electron per lane through mobility steps t_first..pt of the current Poisson step, the whole warp in
+// lockstep: all lanes run the same step t, so the loop is straight-line code -- the Philox block changes for
+// the whole warp at once, lanes that are dead (or, kStaged, not born yet: a child born at step tb takes part
+// from tb+1 on) keep computing values nobody stores instead of branching around the body, and the only
+// branch is the warp vote "somebody spawned".  updateParticle, src/particle_move.cu:22-87.
+template <bool kStaged>
+__device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float& y, float& z, float& vx, float& vy, float& vz,
+                                              const float ax, const float ay, const float az, const unsigned long long id, bool& alive,
+                                              const int tb, const int t_first, int& staged, unsigned& pushes, int& dead) {
+    const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
+    const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
+    const bool was_alive = alive;
+    int t_end = c.pt;                                             // the last step this lane's electron is pushed in
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+    for (int t = t_first; t <= c.pt; ++t) {
+        const unsigned g = c.g0 + (unsigned)t;
+        if (t == t_first || (g & 3u) == 0u)                      // warp-uniform
+            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), c.seed);
+        const bool act = kStaged ? (alive & (t > tb)) : alive;
+        // leapfrog, src/particle_move.cu:22-39
+        float nvx = __fmaf_rn(-ax, hdt, vx), nvy = __fmaf_rn(-ay, hdt, vy), nvz = __fmaf_rn(-az, hdt, vz);
+        const float nx = __fmaf_rn(nvx, dt, x), ny = __fmaf_rn(nvy, dt, y), nz = __fmaf_rn(nvz, dt, z);
+        nvx = __fmaf_rn(-ax, hdt, nvx); nvy = __fmaf_rn(-ay, hdt, nvy); nvz = __fmaf_rn(-az, hdt, nvz);
+        if (!kStaged || act) { x = nx; y = ny; z = nz; vx = nvx; vy = nvy; vz = nvz; }      // (parents: dead lanes just keep computing)
+        // checkOutOfBounds, src/particle_move.cu:41-52 (a NaN coordinate is NOT out of bounds)
+        const bool oob = (x < 0.f) | (x >= sim) | (y < 0.f) | (y >= sim) | (z < 0.f) | (z >= sim);
+        // collider, src/particle_move.cu:55-80
+        const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
+        const float r = __fmul_rn(uniform01((g & 2u) ? w23 : w01), 100.0f);
+        const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
+        const float2 th = c.thr[energy_index(en, c.edge)];
+        const bool coll = act & !oob;
+        const bool spawn = coll & (r < th.x);                    // ionisation
+        const bool die = act & (oob | (!spawn & (r < th.y)));    // left the domain, or attachment
+        const unsigned m = __ballot_sync(kFull, spawn);
+        if (m) {
+            const int cnt = __popc(m);
+            if (staged + cnt > 32) { stage_spill<true>(c, staged); staged = 0; }
+            if (spawn) {                                         // the child copies the pre-flip state
+                uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
+                q[0 * 32] = __float_as_uint(x); q[1 * 32] = __float_as_uint(y); q[2 * 32] = __float_as_uint(z);
+                q[3 * 32] = __float_as_uint(vx); q[4 * 32] = __float_as_uint(vy); q[5 * 32] = __float_as_uint(vz);
+                q[6 * 32] = __float_as_uint(ax); q[7 * 32] = __float_as_uint(ay); q[8 * 32] = __float_as_uint(az);
+                q[9 * 32] = (uint32_t)t;
+                q[10 * 32] = (uint32_t)id; q[11 * 32] = (uint32_t)(id >> 32);
+            }
+            staged += cnt;
+            const uint32_t flip = spawn ? 0x80000000u : 0u;      // parent v = -v
+            vx = __uint_as_float(__float_as_uint(vx) ^ flip);
+            vy = __uint_as_float(__float_as_uint(vy) ^ flip);
+            vz = __uint_as_float(__float_as_uint(vz) ^ flip);
+        }
+        if (die) t_end = t;
+        alive = alive & !die;
+    }
+    pushes += was_alive ? (unsigned)(t_end - tb) : 0u;
+    dead += (was_alive & !alive) ? 1 : 0;
+}
+
 template <bool kLaterGen>
 __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead) {
     const int i = i0 + c.lane;
@@ -548,52 +608,8 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
         gather_field(f, ix, iy, iz, ax, ay, az);
         if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
     }
-    const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
-    const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
     bool alive = was_alive;
-    unsigned g = c.g0;
-    uint4 rnd = make_uint4(0, 0, 0, 0);
-#pragma unroll 1
-    for (int t = 1; t <= c.pt; ++t) {
-        ++g;
-        if (t == 1 || (g & 3u) == 0u)                            // warp-uniform
-            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), c.seed);
-        // leapfrog, src/particle_move.cu:22-39
-        vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
-        x = __fmaf_rn(vx, dt, x); y = __fmaf_rn(vy, dt, y); z = __fmaf_rn(vz, dt, z);
-        vx = __fmaf_rn(-ax, hdt, vx); vy = __fmaf_rn(-ay, hdt, vy); vz = __fmaf_rn(-az, hdt, vz);
-        // checkOutOfBounds, src/particle_move.cu:41-52 (a NaN coordinate is NOT out of bounds)
-        const bool oob = (x < 0.f) | (x >= sim) | (y < 0.f) | (y >= sim) | (z < 0.f) | (z >= sim);
-        // collider, src/particle_move.cu:55-80
-        const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
-        const float r = __fmul_rn(uniform01((g & 2u) ? w23 : w01), 100.0f);
-        const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
-        const float2 th = c.thr[energy_index(en, c.edge)];
-        const bool coll = alive & !oob;
-        const bool spawn = coll & (r < th.x);                    // ionisation
-        const bool die = alive & (oob | (!spawn & (r < th.y)));  // left the domain, or attachment
-        pushes += alive ? 1u : 0u;
-        const unsigned m = __ballot_sync(kFull, spawn);
-        if (m) {
-            const int cnt = __popc(m);
-            if (staged + cnt > 32) { stage_spill<true>(c, staged); staged = 0; }
-            if (spawn) {                                         // the child copies the pre-flip state
-                uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
-                q[0 * 32] = __float_as_uint(x); q[1 * 32] = __float_as_uint(y); q[2 * 32] = __float_as_uint(z);
-                q[3 * 32] = __float_as_uint(vx); q[4 * 32] = __float_as_uint(vy); q[5 * 32] = __float_as_uint(vz);
-                q[6 * 32] = __float_as_uint(ax); q[7 * 32] = __float_as_uint(ay); q[8 * 32] = __float_as_uint(az);
-                q[9 * 32] = (uint32_t)t;
-                q[10 * 32] = (uint32_t)id; q[11 * 32] = (uint32_t)(id >> 32);
-            }
-            staged += cnt;
-            const uint32_t flip = spawn ? 0x80000000u : 0u;      // parent v = -v
-            vx = __uint_as_float(__float_as_uint(vx) ^ flip);
-            vy = __uint_as_float(__float_as_uint(vy) ^ flip);
-            vz = __uint_as_float(__float_as_uint(vz) ^ flip);
-        }
-        dead += die ? 1 : 0;
-        alive = alive & !die;
-    }
+    lockstep_push<false>(c, x, y, z, vx, vy, vz, ax, ay, az, id, alive, 0, 1, staged, pushes, dead);
     if (was_alive) {
         if (alive) {
             __stcg(c.s.x + i, x); __stcg(c.s.y + i, y); __stcg(c.s.z + i, z);
@@ -646,8 +662,8 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
     const bool born = c.lane < k && vslot < c.cap;
     const bool in = born && slot < c.cap;
     bool alive = born;
-    bool touched = false;
-    advance<true>(c, e, alive, tb + 1, c.pt, staged, pushes, dead, touched);
+    const int t_first = __reduce_min_sync(kFull, born ? tb : 0x3fffffff) + 1;
+    lockstep_push<true>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, tb, t_first, staged, pushes, dead);
     if (__any_sync(kFull, born & !in)) {                     // rare: no room above the holes -> parked until this step's compaction
         const bool park = born && !in && alive;
         const unsigned pm = __ballot_sync(kFull, park);
