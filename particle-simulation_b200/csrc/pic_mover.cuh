@@ -563,9 +563,15 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
         if (f.store_acc) { __stcg(c.s.ax + i, e.ax); __stcg(c.s.ay + i, e.ay); __stcg(c.s.az + i, e.az); }
     }
     bool alive = was_alive;
-    const int t0 = max(1, ts + 1);          // src/pic.cu:218
     bool touched = false;
-    advance<true>(c, e, alive, t0, c.pt, staged, pushes, dead, touched);
+    if (kLaterGen) {                        // spilled children (ts = birth step): the lockstep loop, each from its own step on
+        const int t_first = __reduce_min_sync(kFull, was_alive ? ts : 0x3fffffff) + 1;
+        lockstep_push<true>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, ts, t_first, staged, pushes, dead);
+        touched = true;
+    } else {
+        const int t0 = max(1, ts + 1);      // src/pic.cu:218
+        advance<true>(c, e, alive, t0, c.pt, staged, pushes, dead, touched);
+    }
     if (was_alive) {
         if (touched) {
             __stcg(c.s.x + i, e.x); __stcg(c.s.y + i, e.y); __stcg(c.s.z + i, e.z);
