@@ -165,6 +165,19 @@ int picb200_dev_energy_index(int32_t device, int64_t n, const float* energy, int
 /* host-side loader (src/cross_section.cu:3-28): returns rows read, -1 if the file cannot be opened */
 int picb200_load_table(const char* path, float* rows2);
 
+/* ---- snapshots ------------------------------------------------------------ */
+/* image() + save_png() of src/utility.cu:4-74 without libpng: 500 x 500 RGB, an 11 x 11 black square per
+ * electron at pixel (x + i, 500 - (y + j)); host only, no GPU needed.  The CLI writes
+ * ./out/visualization/test_%04d.png and the "Saved image to ..." line at every logged step, as log() does
+ * (src/utility.cu:133), when that directory exists. */
+int picb200_snapshot_png(const float* x, const float* y, int64_t n, const char* path);
+/* Binary snapshot of the population (SoA, optionally sorted by particle id so that equal runs give equal
+ * files) and of the run counters; the reference can only print its state as text (src/utility.cu:124-137)
+ * and cannot restart.  picb200_load_state replaces the population of `sim` (same seed and poisson_timestep
+ * required) and restores Poisson index, totals and push count: the run continues bit for bit. */
+int picb200_save_state(picb200_sim* sim, const char* path, int32_t sorted_by_id);
+int picb200_load_state(picb200_sim* sim, const char* path);
+
 /* ---- multi-GPU over NVLink peer memory (no reference counterpart: device 0 is hard-coded, src/pic.cu:394)
  * With nranks > 1 the modes 30/33 kernel can exchange the charge grid itself, by reading the peers' local
  * grids through NVLink, so that a whole run stays one launch per GPU.  Every rank exports a handle, the

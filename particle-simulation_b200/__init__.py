@@ -113,6 +113,9 @@ SIGNATURES = {
     "picb200_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "picb200_peer_export": (C.c_int, [_sim, C.c_void_p]),
     "picb200_peer_connect": (C.c_int, [_sim, C.c_void_p]),
+    "picb200_snapshot_png": (C.c_int, [_fp, _fp, C.c_int64, C.c_char_p]),
+    "picb200_save_state": (C.c_int, [_sim, C.c_char_p, C.c_int32]),
+    "picb200_load_state": (C.c_int, [_sim, C.c_char_p]),
 }
 for _name, (_res, _args) in SIGNATURES.items():
     _f = getattr(lib, _name)  # AttributeError here = the library does not export what the header declares
@@ -286,6 +289,14 @@ class Sim:
         b = C.create_string_buffer(blob, len(blob))
         _check(lib.picb200_peer_connect(self._h, C.cast(b, C.c_void_p)))
 
+    def save_state(self, path, sorted_by_id=True):
+        """Binary snapshot of the population and the run counters (picb200_save_state)."""
+        _check(lib.picb200_save_state(self._h, os.fsencode(path), 1 if sorted_by_id else 0))
+
+    def load_state(self, path):
+        """Replace the population by a snapshot and continue its run (picb200_load_state)."""
+        _check(lib.picb200_load_state(self._h, os.fsencode(path)))
+
     def profile(self) -> dict:
         p = Profile()
         _check(lib.picb200_get_profile(self._h, C.byref(p)))
@@ -364,6 +375,33 @@ def host_energy_edges():
     e = np.empty(TABLE_ROWS + 1, dtype=np.float32)
     lib.picb200_host_energy_edges(_ptr(e, _fp))
     return e
+
+
+def snapshot_png(x, y, path):
+    """image() of src/utility.cu:52-74 (host only): 500 x 500 PNG, one 11 x 11 black square per electron."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    y = np.ascontiguousarray(y, dtype=np.float32)
+    assert x.shape == y.shape and x.ndim == 1
+    _check(lib.picb200_snapshot_png(_ptr(x, _fp), _ptr(y, _fp), x.size, os.fsencode(path)))
+
+
+def read_state(path):
+    """Parse a picb200_save_state file -> (header dict, dict of arrays)."""
+    raw = open(path, "rb").read()
+    hdr = np.frombuffer(raw[:72], dtype=np.dtype([("magic", "S8"), ("version", "<u4"), ("header_bytes", "<u4"), ("n", "<i8"),
+                                                  ("poisson_index", "<i4"), ("poisson_timestep", "<i4"), ("total_added", "<i8"),
+                                                  ("total_removed", "<i8"), ("pushes", "<u8"), ("seed", "<u8"), ("sorted_by_id", "<i4"),
+                                                  ("reserved", "<i4")]))[0]
+    assert hdr["magic"] == b"PICB200S" and hdr["version"] == 1
+    n, off, out = int(hdr["n"]), int(hdr["header_bytes"]), {}
+    for k in ("x", "y", "z", "vx", "vy", "vz", "ax", "ay", "az"):
+        out[k] = np.frombuffer(raw, dtype="<f4", count=n, offset=off)
+        off += 4 * n
+    out["ts"] = np.frombuffer(raw, dtype="<i4", count=n, offset=off)
+    off += 4 * n
+    out["id"] = np.frombuffer(raw, dtype="<u8", count=n, offset=off)
+    assert off + 8 * n == len(raw)
+    return {k: (hdr[k].item() if k != "magic" else hdr[k]) for k in hdr.dtype.names}, out
 
 
 def host_cell_bounds():

@@ -962,4 +962,5 @@ int picb200_nccl_unique_id(void* out128) {
 
 }  // extern "C"
 
+#include "pic_state.inl"
 #include "pic_run.inl"

@@ -5,8 +5,9 @@
 
 namespace picb200 {
 
-// log() of src/utility.cu:124-137: "Time t, amount n" + one line per electron + blank line.
-// (The PNG snapshot and its "Saved image" line are not produced; see DESIGN.md.)
+// log() of src/utility.cu:124-137: "Time t, amount n" + one line per electron + the PNG snapshot with its
+// "Saved image" line (written when ./out/visualization exists: the reference crashes without it) + blank line.
+// PICB200_DUMP_DIR=<dir> adds a binary snapshot <dir>/state_%04d.bin per logged step (picb200_save_state).
 static int print_state(picb200_sim* sim, int t) {
     Sim& s = sim->s;
     if (s.sync_state()) return 1;
@@ -23,7 +24,19 @@ static int print_state(picb200_sim* sim, int t) {
                (double)b[i], (double)b[n + i], (double)b[2 * n + i], (double)b[3 * n + i], (double)b[4 * n + i],
                (double)b[5 * n + i], b[6 * n + i], b[7 * n + i], b[8 * n + i], ts[i]);
     }
+    char png[64];
+    snprintf(png, sizeof png, "./out/visualization/test_%04d.png", t);       // src/utility.cu:69
+    if (FILE* probe = fopen(png, "wb")) {
+        fclose(probe);
+        if (picb200_snapshot_png(b, b + n, (int64_t)n, png)) return 1;
+        printf("Saved image to %s\n", png);                                  // src/utility.cu:34
+    }
     printf("\n");
+    if (const char* dir = getenv("PICB200_DUMP_DIR")) {
+        char path[4096];
+        snprintf(path, sizeof path, "%s/state_%04d.bin", dir, t);
+        if (picb200_save_state(sim, path, 1)) return 1;
+    }
     return 0;
 }
 
@@ -57,10 +70,13 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
         // particle slab of this rank: ids [rank*init_n/nranks, (rank+1)*init_n/nranks)
         const long long lo = (long long)cfg.init_n * cfg.rank / cfg.nranks;
         const long long hi = (long long)cfg.init_n * (cfg.rank + 1) / cfg.nranks;
-        if (s.init_uniform((int)(hi - lo), (unsigned long long)lo)) break;
+        // PICB200_RESTART=<file>: continue the run a snapshot was taken from (single GPU) instead of seeding a new one
+        const char* restart = cfg.nranks == 1 ? getenv("PICB200_RESTART") : nullptr;
+        if (restart ? picb200_load_state(sim, restart) : s.init_uniform((int)(hi - lo), (unsigned long long)lo)) break;
         if (cudaEventRecord(s.ev_start, s.stream) != cudaSuccess) { fail("event record", "Setup"); break; }
 
-        const int P = cfg.poisson_steps;
+        const int t_begin = restart ? s.h_st->poisson_index : 0;
+        const int P = std::max(0, cfg.poisson_steps - t_begin);     // Poisson steps still to do
         const bool verbose = say && cfg.verbose != 0;
         const bool host_in_loop = verbose || cfg.mode == PICB200_MODE_CPU_SYNC || cfg.mode == PICB200_MODE_NAIVE || cfg.nranks > 1;
         bool failed = false;
@@ -70,17 +86,18 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
             if (s.fused) failed = s.fused_steps(P) != 0;
             else for (int t = 0; t < P && !failed; ++t) failed = s.poisson_step(false) != 0;
             if (failed) break;
-            std::vector<StepLog> lg((size_t)std::max(1, P));
-            if (cudaMemcpyAsync(lg.data(), s.log, sizeof(StepLog) * (size_t)std::max(1, P), cudaMemcpyDeviceToHost, s.stream) != cudaSuccess ||
+            const size_t n_log = (size_t)std::max(1, std::min(cfg.poisson_steps, s.log_len));
+            std::vector<StepLog> lg(n_log);
+            if (cudaMemcpyAsync(lg.data(), s.log, sizeof(StepLog) * n_log, cudaMemcpyDeviceToHost, s.stream) != cudaSuccess ||
                 s.sync_state()) { fail("log readback", "Mobility steps"); break; }
             if (say) {
-                for (int t = 0; t < s.h_st->poisson_index; ++t) {
+                for (int t = t_begin; t < s.h_st->poisson_index && (size_t)t < n_log; ++t) {
                     if (lg[(size_t)t].n_after_mobility >= cfg.capacity) printf("\n\nOVERFLOW FROM ADDING PARTICLES\n\n\n");
                     if (lg[(size_t)t].n_after_compaction == 0) { printf("Hit 0\n"); break; }
                 }
             }
         } else {
-            for (int t = 0; t < P; ++t) {
+            for (int t = t_begin; t < cfg.poisson_steps; ++t) {
                 if (verbose && t % cfg.verbose == 0 && print_state(sim, t)) { failed = true; break; }
                 if (s.poisson_step(true)) { failed = true; break; }
                 if (say && s.h_st->last_n_after_mobility >= cfg.capacity) printf("\n\nOVERFLOW FROM ADDING PARTICLES\n\n\n");
@@ -88,7 +105,7 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
             }
             if (failed) break;
         }
-        if (verbose && P % cfg.verbose == 0 && print_state(sim, P)) break;     // src/pic.cu:561
+        if (verbose && cfg.poisson_steps % cfg.verbose == 0 && print_state(sim, cfg.poisson_steps)) break;     // src/pic.cu:561
         if (cudaEventRecord(s.ev_stop, s.stream) != cudaSuccess || cudaEventSynchronize(s.ev_stop) != cudaSuccess) {
             fail(cudaGetErrorString(cudaGetLastError()), "After sim");
             break;
@@ -98,6 +115,8 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
         s.gpu_ms = ms;
         picb200_summary sum;
         if (picb200_get_summary(sim, &sum)) break;
+        // PICB200_DUMP_FINAL=<file>: binary snapshot of the final state (no text dump needed; restart with PICB200_RESTART)
+        if (const char* fin = getenv("PICB200_DUMP_FINAL")) { if (picb200_save_state(sim, fin, 1)) break; }
         if (electrons_out && electrons_cap > 0) {
             int64_t got = 0;
             if (picb200_download_aos(sim, electrons_out, electrons_cap, &got)) break;
