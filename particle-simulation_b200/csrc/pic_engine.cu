@@ -313,8 +313,10 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMemsetAsync(log, 0, sizeof(StepLog) * (size_t)log_len, stream), "Minor alloc");
 
     CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
     fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
@@ -597,7 +599,7 @@ int Sim::fused_steps(int steps) {
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
-                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, compact_policy};
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
@@ -608,7 +610,10 @@ int Sim::fused_steps(int steps) {
         }
         void* args[] = {&a};
         span_begin(kPhMover);
-        CK(cudaLaunchCooperativeKernel(peer ? (const void*)k_poisson_fused<true> : (const void*)k_poisson_fused<false>, dim3((unsigned)sm_count),
+        const bool adopt = cfg.poisson_timestep >= kAdoptMinSteps;
+        const void* kern = peer ? (adopt ? (const void*)k_poisson_fused<true, true> : (const void*)k_poisson_fused<true, false>)
+                                : (adopt ? (const void*)k_poisson_fused<false, true> : (const void*)k_poisson_fused<false, false>);
+        CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)sm_count),
                                        dim3((unsigned)mover_threads), args, (size_t)kFusedSmemBytes(mover_threads), stream),
            "Mobility steps");
         ++launches; ++mover_launches;

@@ -45,6 +45,7 @@ struct MoverCtx {
     const float* edge;
     uint32_t* stage;
     int cap, pt, lane, stepwise;
+    int adopt_min;       // fused kernel, adopting loop: dead lanes in the warp from which children are handed over
     int* pool;           // fused kernel: free slots this warp has come across in the current Poisson step (shared memory)
     unsigned g0;
     uint2 seed;
@@ -372,6 +373,7 @@ struct FusedArgs {
     int initial_deposit;         // kPeer only: no summed grid holds this population yet
     Soa park;                    // parking area for step_end_fused's rare case (park_cap electrons)
     int park_cap;
+    int adopt_min;               // kAdoptMin, or PICB200_ADOPT_MIN (33: never)
     int compact_policy;          // 0: lazy (default); 1: after every Poisson step (PICB200_COMPACT=eager); 2: lazy, no capacity guard (tests)
 };
 
@@ -487,20 +489,32 @@ __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, 
 // the whole warp at once, lanes that are dead (or, kStaged, not born yet: a child born at step tb takes part
 // from tb+1 on) keep computing values nobody stores instead of branching around the body, and the only
 // branch is the warp vote "somebody spawned".  updateParticle, src/particle_move.cu:22-87.
-template <bool kStaged>
+//
+// kAdopt (chunks of the store): once kAdoptMin lanes of the warp are dead, a child is handed to a dead lane
+// the moment it is born instead of being staged -- it needs exactly the steps the loop still has to run --
+// and later takes over that lane's slot.  In collision-heavy runs (poisson_timestep = 100: every electron is
+// replaced 2.8 times per Poisson step) this keeps the lanes busy; the Philox blocks are then refreshed for
+// the whole warp, because the new occupants have other ids.  `slot_ok`: the lane has a slot to offer.
+constexpr int kAdoptMin = 8;
+constexpr int kAdoptMinSteps = 24;   // poisson_timestep from which chunks use the adopting loop
+template <bool kStaged, bool kAdopt>
 __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float& y, float& z, float& vx, float& vy, float& vz,
-                                              const float ax, const float ay, const float az, const unsigned long long id, bool& alive,
-                                              const int tb, const int t_first, int& staged, unsigned& pushes, int& dead) {
+                                              float& ax, float& ay, float& az, unsigned long long& id, bool& alive,
+                                              int tb, const int t_first, int& staged, unsigned& pushes, int& dead,
+                                              const bool slot_ok, int& n_adopted) {
     const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
     const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
-    const bool was_alive = alive;
-    int t_end = c.pt;                                             // the last step this lane's electron is pushed in
     uint4 rnd = make_uint4(0, 0, 0, 0);
+    bool refresh = false;
+    const bool was_alive = alive;
+    int t_end = c.pt;                                             // !kAdopt: the last step this lane's electron is pushed in
 #pragma unroll 1
     for (int t = t_first; t <= c.pt; ++t) {
         const unsigned g = c.g0 + (unsigned)t;
-        if (t == t_first || (g & 3u) == 0u)                      // warp-uniform
+        if (t == t_first || (g & 3u) == 0u || (kAdopt && refresh)) {         // warp-uniform
             rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), c.seed);
+            refresh = false;
+        }
         const bool act = kStaged ? (alive & (t > tb)) : alive;
         // leapfrog, src/particle_move.cu:22-39
         float nvx = __fmaf_rn(-ax, hdt, vx), nvy = __fmaf_rn(-ay, hdt, vy), nvz = __fmaf_rn(-az, hdt, vz);
@@ -517,29 +531,60 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
         const bool coll = act & !oob;
         const bool spawn = coll & (r < th.x);                    // ionisation
         const bool die = act & (oob | (!spawn & (r < th.y)));    // left the domain, or attachment
-        const unsigned m = __ballot_sync(kFull, spawn);
+        if (kAdopt) { if (die) { pushes += (unsigned)(t - tb); ++dead; } }       // it was pushed in steps tb+1 .. t
+        else if (die) t_end = t;
+        alive = alive & !die;
+        unsigned m = __ballot_sync(kFull, spawn);
         if (m) {
-            const int cnt = __popc(m);
-            if (staged + cnt > 32) { stage_spill<true>(c, staged); staged = 0; }
-            if (spawn) {                                         // the child copies the pre-flip state
-                uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
-                q[0 * 32] = __float_as_uint(x); q[1 * 32] = __float_as_uint(y); q[2 * 32] = __float_as_uint(z);
-                q[3 * 32] = __float_as_uint(vx); q[4 * 32] = __float_as_uint(vy); q[5 * 32] = __float_as_uint(vz);
-                q[6 * 32] = __float_as_uint(ax); q[7 * 32] = __float_as_uint(ay); q[8 * 32] = __float_as_uint(az);
-                q[9 * 32] = (uint32_t)t;
-                q[10 * 32] = (uint32_t)id; q[11 * 32] = (uint32_t)(id >> 32);
+            bool stage_it = spawn;
+            if (kAdopt) {
+                const bool free_lane = slot_ok & !alive;         // dead before this step, or died in it
+                const unsigned fm = __ballot_sync(kFull, free_lane);
+                if (__popc(fm) >= c.adopt_min) {
+                    const int na = min(__popc(m), __popc(fm));   // the first na spawners hand over to the first na free lanes
+                    const int my_free = __popc(fm & lanemask_lt());
+                    const bool adopt = free_lane && my_free < na;
+                    const int src = (int)__fns(m, 0, my_free + 1) & 31;
+                    const float cx = __shfl_sync(kFull, x, src), cy = __shfl_sync(kFull, y, src), cz = __shfl_sync(kFull, z, src);
+                    const float cvx = __shfl_sync(kFull, vx, src), cvy = __shfl_sync(kFull, vy, src), cvz = __shfl_sync(kFull, vz, src);   // pre-flip
+                    const float cax = __shfl_sync(kFull, ax, src), cay = __shfl_sync(kFull, ay, src), caz = __shfl_sync(kFull, az, src);
+                    const unsigned long long pid = __shfl_sync(kFull, id, src);
+                    if (adopt) {
+                        x = cx; y = cy; z = cz; vx = cvx; vy = cvy; vz = cvz; ax = cax; ay = cay; az = caz;
+                        id = child_id(pid, (unsigned long long)g);
+                        alive = true; tb = t; ++n_adopted;
+                    }
+                    const int my_spawn = __popc(m & lanemask_lt());
+                    stage_it = spawn && my_spawn >= na;
+                    refresh = true;                              // new ids in the warp: their Philox blocks, from the next step on
+                }
             }
-            staged += cnt;
+            const unsigned sm = kAdopt ? __ballot_sync(kFull, stage_it) : m;
+            if (sm) {
+                const int cnt = __popc(sm);
+                if (staged + cnt > 32) { stage_spill<true>(c, staged); staged = 0; }
+                if (stage_it) {                                  // the child copies the pre-flip state
+                    uint32_t* q = c.stage + staged + __popc(sm & lanemask_lt());
+                    q[0 * 32] = __float_as_uint(x); q[1 * 32] = __float_as_uint(y); q[2 * 32] = __float_as_uint(z);
+                    q[3 * 32] = __float_as_uint(vx); q[4 * 32] = __float_as_uint(vy); q[5 * 32] = __float_as_uint(vz);
+                    q[6 * 32] = __float_as_uint(ax); q[7 * 32] = __float_as_uint(ay); q[8 * 32] = __float_as_uint(az);
+                    q[9 * 32] = (uint32_t)t;
+                    q[10 * 32] = (uint32_t)id; q[11 * 32] = (uint32_t)(id >> 32);
+                }
+                staged += cnt;
+            }
             const uint32_t flip = spawn ? 0x80000000u : 0u;      // parent v = -v
             vx = __uint_as_float(__float_as_uint(vx) ^ flip);
             vy = __uint_as_float(__float_as_uint(vy) ^ flip);
             vz = __uint_as_float(__float_as_uint(vz) ^ flip);
         }
-        if (die) t_end = t;
-        alive = alive & !die;
     }
-    pushes += was_alive ? (unsigned)(t_end - tb) : 0u;
-    dead += (was_alive & !alive) ? 1 : 0;
+    if (kAdopt) {
+        if (alive) pushes += (unsigned)(c.pt - tb);
+    } else {
+        pushes += was_alive ? (unsigned)(t_end - tb) : 0u;
+        dead += (was_alive & !alive) ? 1 : 0;
+    }
 }
 
 template <bool kLaterGen>
@@ -566,7 +611,8 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
     bool touched = false;
     if (kLaterGen) {                        // spilled children (ts = birth step): the lockstep loop, each from its own step on
         const int t_first = __reduce_min_sync(kFull, was_alive ? ts : 0x3fffffff) + 1;
-        lockstep_push<true>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, ts, t_first, staged, pushes, dead);
+        int none = 0;
+        lockstep_push<true, false>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, ts, t_first, staged, pushes, dead, false, none);
         touched = true;
     } else {
         const int t0 = max(1, ts + 1);      // src/pic.cu:218
@@ -589,6 +635,7 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
 // mobility step t, so the step loop is straight-line code: the Philox block changes for the whole
 // warp at once, dead lanes keep computing values nobody stores instead of branching around the body,
 // and the only branch is the warp vote "somebody spawned".
+template <bool kAdopt>
 __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead, int& npool) {
     const int i = i0 + c.lane;
     const bool in = i < end;
@@ -615,12 +662,30 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
         if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
     }
     bool alive = was_alive;
-    lockstep_push<false>(c, x, y, z, vx, vy, vz, ax, ay, az, id, alive, 0, 1, staged, pushes, dead);
-    if (was_alive) {
+    int n_adopted = 0;                                            // children this lane took over from their parents' lanes
+    lockstep_push<false, kAdopt>(c, x, y, z, vx, vy, vz, ax, ay, az, id, alive, 0, 1, staged, pushes, dead, in, n_adopted);
+    if (kAdopt && __any_sync(kFull, n_adopted > 0)) {
+        // adopted children were born like any other: the reference's counter n decides whether they exist
+        // (src/pic.cu:222).  One atomic per chunk; the lane's LAST adoption has the highest index, the
+        // earlier ones have died.  An index >= capacity can only come up in a run that overflows: those
+        // children never existed -- their deaths are taken back and a survivor is dropped.
+        int incl = n_adopted;
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(kFull, incl, o); if (c.lane >= o) incl += u; }
+        int vbase, tbase;
+        reserve_fused(c, __shfl_sync(kFull, incl, 31), 0, vbase, tbase);
+        const int over = min(n_adopted, max(0, vbase + incl - c.cap));
+        if (over > 0) { dead -= over - (alive ? 1 : 0); alive = false; }
+    }
+    if (in) {
         if (alive) {
             __stcg(c.s.x + i, x); __stcg(c.s.y + i, y); __stcg(c.s.z + i, z);
             __stcg(c.s.vx + i, vx); __stcg(c.s.vy + i, vy); __stcg(c.s.vz + i, vz);
-        } else {
+            if (kAdopt && n_adopted > 0) {                        // a child lives in this slot now
+                __stcg(c.s.id + i, id);
+                if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
+                if (!was_alive) __stcg(c.s.ts + i, -1);
+            }
+        } else if (was_alive) {
             __stcg(c.s.ts + i, kDead);
         }
     }
@@ -669,7 +734,8 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
     const bool in = born && slot < c.cap;
     bool alive = born;
     const int t_first = __reduce_min_sync(kFull, born ? tb : 0x3fffffff) + 1;
-    lockstep_push<true>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, tb, t_first, staged, pushes, dead);
+    int none = 0;
+    lockstep_push<true, false>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, tb, t_first, staged, pushes, dead, false, none);
     if (__any_sync(kFull, born & !in)) {                     // rare: no room above the holes -> parked until this step's compaction
         const bool park = born && !in && alive;
         const unsigned pm = __ballot_sync(kFull, park);
@@ -702,7 +768,9 @@ constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
 constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPushStageBytesPerWarp + kPoolSlots * 4); }
 
-template <bool kPeer>
+// kAdopt: the chunks use the adopting step loop (lockstep_push); the host picks it for poisson_timestep >= kAdoptMinSteps --
+// it carries more state through every step and only pays when lanes die out long before the Poisson step ends.
+template <bool kPeer, bool kAdopt>
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_box[6];
@@ -730,6 +798,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     c.pt = a.pt;
     c.lane = threadIdx.x & 31;
     c.stepwise = 0;
+    c.adopt_min = a.adopt_min;
     c.seed = a.seed;
     FusedCtx f;
     f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
@@ -858,7 +927,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             if (c.lane == 0) k = atomicAdd(&s_ticket, 1);
             const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
             if (chunk >= chunks) break;
-            fused_chunk_fast(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
+            fused_chunk_fast<kAdopt>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
             if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead, npool);
         }
         while (staged) fused_staged(c, f, staged, pushes, dead, npool);

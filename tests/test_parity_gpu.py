@@ -363,6 +363,44 @@ def test_lazy_compaction_parks_children_near_capacity(engine, oracle):
             assert lazy[:4] == (c["n"], c["added"], c["removed"], c["pushes"])
 
 
+@pytest.mark.parametrize("pt,split,remove", [(64, 2.5, 2.5), (100, 3.0, 2.0), (32, 1.0, 6.0)])
+def test_adopting_step_loop_matches_oracle(engine, oracle, pt, split, remove):
+    """poisson_timestep >= 24 selects the kernel whose step loop hands a new-born child to a dead lane of the
+    warp on the spot (lockstep_push, kAdopt): with several per cent of split / remove per push every lane changes
+    its occupant a few times per Poisson step.  Same electrons, bit for bit, as the oracle and as mode 31."""
+    rows = np.tile(np.array([[split, remove]], dtype=np.float32), (10000, 1))
+    n, P, cap = 20000, 3, 3000000        # (3.0, 2.0) x 100 pushes: the reference's counter n peaks at 30 x the start
+    pos, vel = hot_state(n, seed=31)
+    o = oracle.Oracle(capacity=cap, poisson_timestep=pt, table_rows=rows, threads=4)
+    o.upload(*pos, *vel)
+    o.run(P)
+    c, s = o.counters(), o.download_sorted()
+    assert c["added"] > n // 8 and c["removed"] > n // 2     # lanes die out and are handed children: the adoption path is busy
+    assert o.counters()["n"] + c["added"] < cap              # (no overflow: which child is dropped would be a race)
+    for mode in (0, 1):
+        with engine.Sim(capacity=cap, poisson_timestep=pt, mode=mode, table_rows=rows, poisson_steps=P) as sim:
+            sim.upload(*pos, *vel)
+            sim.run_steps(P)
+            m = sim.summary()
+            assert (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"]), mode
+            assert_state_equal(sim.download(), s)
+
+
+def test_adopting_step_loop_capacity_overflow(engine):
+    """Adopted children ask the reference's counter n for their existence only when their chunk ends; in a run
+    that overflows those past the capacity are taken back.  Conservation must hold whatever the race."""
+    rows = np.tile(np.array([[4.0, 1.0]], dtype=np.float32), (10000, 1))
+    pos, vel = hot_state(5000, seed=32)
+    with engine.Sim(capacity=9000, poisson_timestep=64, mode=0, table_rows=rows, poisson_steps=3) as sim:
+        sim.upload(*pos, *vel)
+        sim.run_steps(3)
+        m = sim.summary()
+        assert m["overflowed"] >= 1 and m["final_n"] <= 9000
+        assert m["final_n"] == 5000 + m["total_added"] - m["total_removed"]
+        d = sim.download()
+        assert d.n == m["final_n"] and np.all(d.ts == -1) and len(np.unique(d.id)) == d.n
+
+
 # ------------------------------------------------------------------------------------------
 # the outer boundary: the `run` CLI and its stdout contract
 # ------------------------------------------------------------------------------------------
