@@ -490,12 +490,12 @@ __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, 
 // from tb+1 on) keep computing values nobody stores instead of branching around the body, and the only
 // branch is the warp vote "somebody spawned".  updateParticle, src/particle_move.cu:22-87.
 //
-// kAdopt (chunks of the store): once kAdoptMin lanes of the warp are dead, a child is handed to a dead lane
+// kAdopt (chunks of the store): while kAdoptMin or more lanes of the warp are dead, a child is handed to a dead lane
 // the moment it is born instead of being staged -- it needs exactly the steps the loop still has to run --
 // and later takes over that lane's slot.  In collision-heavy runs (poisson_timestep = 100: every electron is
 // replaced 2.8 times per Poisson step) this keeps the lanes busy; the Philox blocks are then refreshed for
 // the whole warp, because the new occupants have other ids.  `slot_ok`: the lane has a slot to offer.
-constexpr int kAdoptMin = 8;
+constexpr int kAdoptMin = 1;        // measured at cfg5, poisson_timestep = 100: 1 -> 114 ms, 4 -> 122, 8 -> 132, never -> 163
 constexpr int kAdoptMinSteps = 24;   // poisson_timestep from which chunks use the adopting loop
 template <bool kStaged, bool kAdopt>
 __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float& y, float& z, float& vx, float& vy, float& vz,
