@@ -610,7 +610,7 @@ int Sim::fused_steps(int steps) {
         }
         void* args[] = {&a};
         span_begin(kPhMover);
-        const bool adopt = cfg.poisson_timestep >= kAdoptMinSteps;
+        const bool adopt = cfg.poisson_timestep >= (getenv("PICB200_ADOPT_STEPS") ? atoi(getenv("PICB200_ADOPT_STEPS")) : kAdoptMinSteps);
         const void* kern = peer ? (adopt ? (const void*)k_poisson_fused<true, true> : (const void*)k_poisson_fused<true, false>)
                                 : (adopt ? (const void*)k_poisson_fused<false, true> : (const void*)k_poisson_fused<false, false>);
         CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)sm_count),
