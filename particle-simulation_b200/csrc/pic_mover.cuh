@@ -64,7 +64,7 @@ __device__ __forceinline__ int reserve_slots(const MoverCtx& c, int count) {
 // word: decides which children exist, src/pic.cu:222) and the mark (high word).
 constexpr int kPoolSlots = 64;
 __device__ __forceinline__ void reserve_fused(const MoverCtx& c, int count, int from_top, int& vbase, int& tbase) {
-    unsigned long long old = (unsigned long long)(unsigned)c.cap;           // exhausted: nobody is born
+    unsigned long long old = (unsigned long long)(unsigned)c.cap | ((unsigned long long)(unsigned)c.cap << 32);   // exhausted: nobody is born, no slot is taken
     if (c.lane == 0 && ld_volatile_i32(&c.st->n_alloc) < c.cap)
         old = atomicAdd(reinterpret_cast<unsigned long long*>(&c.st->n_alloc), (unsigned long long)(unsigned)count | ((unsigned long long)(unsigned)from_top << 32));
     old = __shfl_sync(kFull, old, 0);
@@ -89,6 +89,7 @@ __device__ __forceinline__ void stage_spill(const MoverCtx& c, int count) {
         reserve_fused(c, count, count, vslot, slot);
         vslot += c.lane; slot += c.lane;
         if (c.lane < count && vslot < c.cap && slot >= c.cap) *(volatile int*)&c.st->error = 3;   // unfinished children cannot be parked
+        if (c.lane < count && vslot >= c.cap && slot < c.cap) __stcg(c.s.ts + slot, kDead);       // a slot above the mark nobody was born into: a hole
     } else {
         vslot = slot = reserve_slots(c, count) + c.lane;
     }
@@ -732,6 +733,7 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
     __syncwarp();                                            // pool entries read before anybody adds new ones
     const bool born = c.lane < k && vslot < c.cap;
     const bool in = born && slot < c.cap;
+    if (c.lane >= p && c.lane < k && !born && slot < c.cap) __stcg(c.s.ts + slot, kDead);   // (overflow) a slot above the mark nobody was born into: a hole
     bool alive = born;
     const int t_first = __reduce_min_sync(kFull, born ? tb : 0x3fffffff) + 1;
     int none = 0;

@@ -391,14 +391,25 @@ def test_adopting_step_loop_capacity_overflow(engine):
     that overflows those past the capacity are taken back.  Conservation must hold whatever the race."""
     rows = np.tile(np.array([[4.0, 1.0]], dtype=np.float32), (10000, 1))
     pos, vel = hot_state(5000, seed=32)
-    with engine.Sim(capacity=9000, poisson_timestep=64, mode=0, table_rows=rows, poisson_steps=3) as sim:
-        sim.upload(*pos, *vel)
-        sim.run_steps(3)
-        m = sim.summary()
-        assert m["overflowed"] >= 1 and m["final_n"] <= 9000
-        assert m["final_n"] == 5000 + m["total_added"] - m["total_removed"]
-        d = sim.download()
-        assert d.n == m["final_n"] and np.all(d.ts == -1) and len(np.unique(d.id)) == d.n
+    for pt, policy in ((64, None), (64, "eager"), (10, None), (10, "noguard")):     # adopting / plain step loop, lazy / eager compaction
+        old = os.environ.get("PICB200_COMPACT")
+        if policy:
+            os.environ["PICB200_COMPACT"] = policy
+        try:
+            for rep in range(3):                               # which children are dropped is a race: a few rolls of the dice
+                with engine.Sim(capacity=9000, poisson_timestep=pt, mode=0, table_rows=rows, poisson_steps=4) as sim:
+                    sim.upload(*pos, *vel)
+                    sim.run_steps(4)
+                    m = sim.summary()
+                    assert m["overflowed"] >= 1 and m["final_n"] <= 9000
+                    assert m["final_n"] == 5000 + m["total_added"] - m["total_removed"]
+                    d = sim.download()
+                    assert d.n == m["final_n"] and np.all(d.ts == -1), (pt, policy)
+                    assert len(np.unique(d.id)) == d.n, (pt, policy, d.n - len(np.unique(d.id)))    # nobody twice
+        finally:
+            os.environ.pop("PICB200_COMPACT", None)
+            if old is not None:
+                os.environ["PICB200_COMPACT"] = old
 
 
 # ------------------------------------------------------------------------------------------
