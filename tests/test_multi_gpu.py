@@ -63,11 +63,11 @@ def need_gpus(engine, k):
         pytest.skip(f"needs {k} CUDA devices, {engine.device_count()} visible")
 
 
-@pytest.mark.parametrize("transport", ["peer", "nccl"])
+@pytest.mark.parametrize("transport,pt", [("peer", 10), ("nccl", 10), ("peer", 32)])      # pt 32: the adopting step loop
 @pytest.mark.parametrize("k", [2])
-def test_slabs_equal_single_population_oracle(engine, oracle, transport, k):
+def test_slabs_equal_single_population_oracle(engine, oracle, transport, pt, k):
     need_gpus(engine, k)
-    n, pt, cap = 40000, 10, 400000
+    n, cap = 40000, 800000
     rng = np.random.default_rng(3)
     pos = rng.uniform(2.45, 2.65, size=(3, n)).astype(np.float32)     # dense: ~5 electrons per cell, real fields
     vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)          # hot: collisions from the first push

@@ -10,14 +10,18 @@ names = ["own chunks of warp 0 (0->1)", "wait for block's other warps (1->2)", "
 good = t[:, 0, 7] > 0
 t = t[good]
 dur = (t[:, :, 7].max(1) - t[:, :, 0].min(1)) / 1e3
-comp = t[:, 0, 5] > 0          # steps that ended with a compaction (the others leave their holes in place)
+comp = t[:, 0, 6] > 0          # steps that ended with a compaction (the others leave their holes in place)
 print(f"{t.shape[0]} steps x {blocks} blocks; step time (first start -> last end), us: median {np.median(dur):.1f} mean {dur.mean():.1f}"
       f"; {int(comp.sum())} steps with compaction (mean {dur[comp].mean() if comp.any() else 0:.1f}), {int((~comp).sum())} without (mean {dur[~comp].mean() if (~comp).any() else 0:.1f})")
 tl = t[~comp]
 if tl.shape[0]:
-    for nm, a_, b_ in (("own chunks of warp 0 (0->1)", 0, 1), ("wait for block's other warps (1->2)", 1, 2), ("barrier 1 + bookkeeping (2->3)", 2, 3)):
+    rows = [("own chunks of warp 0 (0->1)", 0, 1), ("wait for block's other warps (1->2)", 1, 2), ("barrier 1 + bookkeeping (2->3)", 2, 3)]
+    if tl[:, :, 5].min() > 0:      # peer mode: the exchange follows barrier 1 in every step
+        rows += [("peer: push rows to the peers (3->11)", 3, 11), ("peer: clear own old grid (11->8)", 11, 8), ("peer: drain bulk adds (8->4)", 8, 4),
+                 ("peer: barrier 2 = flag up + wait for peers (4->5)", 4, 5)]
+    for nm, a_, b_ in rows:
         d = (tl[:, :, b_] - tl[:, :, a_]) / 1e3
-        print(f"  [no compaction] {nm:36s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
+        print(f"  [no compaction] {nm:50s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
 t = t[comp]
 if not t.shape[0]:
     sys.exit(0)
