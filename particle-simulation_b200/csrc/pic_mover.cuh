@@ -924,15 +924,18 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // so every SM gets the same number of chunks to within one; inside the block the warps draw
         // their next chunk from a shared-memory ticket, which evens out the children they pick up
         f.store_acc = last_step;
-        for (;;) {
-            int k = 0;
-            if (c.lane == 0) k = atomicAdd(&s_ticket, 1);
-            const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
-            if (chunk >= chunks) break;
-            fused_chunk_fast<kAdopt>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
-            if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead, npool);
+        // (one copy of each of the two code paths in the instruction stream: the loop runs until the tickets
+        // are gone AND the stage is empty)
+        for (bool more = true; more || staged;) {
+            if (more) {
+                int k = 0;
+                if (c.lane == 0) k = atomicAdd(&s_ticket, 1);
+                const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
+                more = chunk < chunks;
+                if (more) fused_chunk_fast<kAdopt>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
+            }
+            if (staged >= kDrainThreshold || (!more && staged)) fused_staged(c, f, staged, pushes, dead, npool);
         }
-        while (staged) fused_staged(c, f, staged, pushes, dead, npool);
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
         if (!kPeer) clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
