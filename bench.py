@@ -124,6 +124,13 @@ def all_sum(dist, v):
     return float(t.item())
 
 
+def ncu_capture():
+    """The committed ncu capture of the dominant kernel (profiles/*_ncu_traffic.json), or None."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_traffic.json")))
+    return json.load(open(files[-1])) if files else None
+
+
 def ncu_traffic(pushes_per_launch):
     """DRAM bytes of one k_poisson_fused launch of this bench: dram__bytes_read.sum + dram__bytes_write.sum of the committed
     `ncu --set full` capture (profiles/*_ncu_traffic.json, written by tools/refresh_profiles.sh), scaled from the captured
@@ -138,6 +145,15 @@ def ncu_traffic(pushes_per_launch):
     per_push = (t["dram_bytes_read"] + t["dram_bytes_write"]) / t["pushes_in_launch"]
     return per_push * pushes_per_launch, (f"{os.path.basename(files[-1])} (commit {t['commit']}): {per_push:.2f} B of DRAM traffic per push in the captured launch "
                                           f"x {pushes_per_launch:.4g} pushes per launch here; bytes")
+
+
+def issue_note():
+    """What actually limits the kernel (it moves < 1 B per push through DRAM): instruction issue, from the ncu capture."""
+    t = ncu_capture()
+    if not t or not t.get("warp_instructions") or not t.get("pushes_in_launch"):
+        return None
+    return {"warp_instructions_per_push": t["warp_instructions"] / t["pushes_in_launch"], "issue_active_pct_whole_launch": t.get("issue_active_pct"),
+            "registers_per_thread": t.get("registers_per_thread"), "source": f"profiles ncu capture, commit {t['commit']}"}
 
 
 def cpu_baseline(budget_s=12.0):
@@ -274,6 +290,7 @@ def run_ours(args):
                      "kernel": "k_poisson_fused", "launches": int(prof["mover_launches"]), "kernel_ms_total": prof["mover_ms"],
                      "kernel_share_of_step": prof["mover_ms"] / gpu_ms if gpu_ms else None,
                      "accounting": f"{BYTES_PER_PUSH:.0f} B per push x pushes per launch (SURVEY.md 8d); peak = {peak_src}; electrons stay in registers for all 10 mobility steps of a launch, so required HBM traffic is ~7.6 B/push and the 68-B-accounted figure may exceed the peak"},
+        "issue_bound_note": issue_note(),
         "phases_ms_per_step": {k: v for k, v in phases.items() if k.endswith("_ms")},
         "clocks": clocks,
     }

@@ -20,7 +20,7 @@ def val(k):
 m = re.search(r'pushes_in_profiled_launch (\d+)', open('gpurun_out/plain_prof.log').read())
 out = {'commit': H, 'kernel': 'k_poisson_fused', 'command': 'tools/prof_run.py 0 1000000 10 10 4000000 30',
        'dram_bytes_read': val('dram__bytes_read.sum'), 'dram_bytes_write': val('dram__bytes_write.sum'),
-       'pushes_in_launch': int(m.group(1)) if m else None, 'duration_ms': float(r[Hd.index('gpu__time_duration.sum')]) * {'ns': 1e-6, 'us': 1e-3, 'ms': 1.0, 's': 1e3}.get(units[Hd.index('gpu__time_duration.sum')], 1.0)}
+       'pushes_in_launch': int(m.group(1)) if m else None, 'warp_instructions': float(r[Hd.index('smsp__inst_executed.sum')]), 'issue_active_pct': float(r[Hd.index('smsp__issue_active.avg.pct_of_peak_sustained_active')]), 'registers_per_thread': float(r[Hd.index('launch__registers_per_thread')]), 'duration_ms': float(r[Hd.index('gpu__time_duration.sum')]) * {'ns': 1e-6, 'us': 1e-3, 'ms': 1.0, 's': 1e3}.get(units[Hd.index('gpu__time_duration.sum')], 1.0)}
 json.dump(out, open(f'profiles/{R}_ncu_traffic.json', 'w'), indent=1)
 print(out)
 PY
