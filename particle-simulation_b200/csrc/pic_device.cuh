@@ -57,6 +57,7 @@ struct DevState {
     int scan_S, scan_D;     // its arguments: slots to look at, dead ones among them
     int parked;             // children of this step waiting for the compaction to make room (see FusedArgs::park)
     int error;              // 2: more children parked than the parking area holds, 3: a spilled child found no slot
+    int win_hi;             // mode 32: electrons that exist when a mobility step starts (k_freeze_window)
     // -- hot atomics, one 128-byte line each so they do not serialise behind one another in L2
     alignas(128) int n_alloc;                   // the reference's counter n during the mobility phase (may overshoot capacity)
     int top_alloc;                              // fused kernel: slots taken above the high-water mark; the two form ONE 64-bit
@@ -379,6 +380,9 @@ __global__ void k_compact_move(Soa s, const DevState* st, const int* __restrict_
 }
 
 // Bookkeeping the reference does on the host after each phase (src/pic.cu:539-559), on the device.
+// Mode 32 (src/pic.cu:524-532) launches one kernel per mobility step over the electrons that exist when the step
+// starts; the reference reads that count back to the host before every launch, here it stays on the device.
+__global__ void k_freeze_window(DevState* st, int capacity) { st->win_hi = min(st->n_alloc, capacity); }
 __global__ void k_mobility_begin(DevState* st) {
     st->n_alloc = st->n;
     st->top_alloc = st->n;

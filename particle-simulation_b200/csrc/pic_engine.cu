@@ -519,9 +519,10 @@ int Sim::op_mobility_begin() {
 }
 
 int Sim::launch_mover_window(int lo, int hi, int t_from, int t_to, bool stepwise) {
-    if (hi <= lo) return 0;
+    if (hi >= 0 && hi <= lo) return 0;
     MoverArgs a{soa, st, tables, cfg.capacity, cfg.poisson_timestep, lo, hi, t_from, t_to, stepwise ? 1 : 0, seed};
-    const int blocks = std::max(1, std::min(sm_count, (hi - lo + mover_threads - 1) / mover_threads));
+    // hi < 0: the window ends at DevState::win_hi, which the host does not know: a full grid, grid-stride loop
+    const int blocks = hi < 0 ? sm_count : std::max(1, std::min(sm_count, (hi - lo + mover_threads - 1) / mover_threads));
     span_begin(kPhMover);
     k_mover<false><<<blocks, mover_threads, kMoverSmemBytes(mover_threads), stream>>>(a);
     ++launches; ++mover_launches;
@@ -556,13 +557,17 @@ int Sim::op_mobility() {
             }
             break;
         }
-        case PICB200_MODE_NAIVE: {         // src/pic.cu:524-532: one launch and one read of n per mobility step
-            if (sync_state()) return 1;
+        case PICB200_MODE_NAIVE: {         // src/pic.cu:524-532: one launch per mobility step
+            // The reference copies n to the host before every launch; here the window of a step is frozen on the
+            // device (k_freeze_window) and the host only looks when a logger wants the state.
             for (int t = 1; t <= pt; ++t) {
-                const int n_host = std::min(h_st->n_alloc, cfg.capacity);
-                if (launch_mover_window(0, n_host, t, t, true)) return 1;
-                if (sync_state()) return 1;
-                if (naive_hook) naive_hook(this, naive_hook_user);
+                k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity);
+                ++launches;
+                if (launch_mover_window(0, -1, t, t, true)) return 1;
+                if (naive_hook) {
+                    if (sync_state()) return 1;
+                    naive_hook(this, naive_hook_user);
+                }
             }
             break;
         }
@@ -784,7 +789,7 @@ int picb200_run_steps(picb200_sim* sim, int32_t steps) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
     CK(cudaEventRecord(s.ev_start, s.stream), "Setup");
-    const bool host_in_loop = s.cfg.mode == PICB200_MODE_CPU_SYNC || s.cfg.mode == PICB200_MODE_NAIVE || s.cfg.nranks > 1;
+    const bool host_in_loop = s.cfg.mode == PICB200_MODE_CPU_SYNC || s.cfg.nranks > 1;
     if (s.fused) {
         if (s.fused_steps(steps)) return 1;
     } else {

@@ -321,10 +321,12 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
             lo = hi;
         }
     } else {
-        const int span = a.hi - a.lo;
+        // hi < 0: the window is [0, win_hi), frozen on the device by k_freeze_window (mode 32 without a host read per step)
+        const int w_hi = a.hi < 0 ? ld_volatile_i32(&a.st->win_hi) : a.hi;
+        const int span = w_hi - a.lo;
         const int rounded = (span + 31) & ~31;
         for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x)
-            process_chunk<false, false>(c, a.lo + k, a.hi, a.t_from, a.t_to, staged, pushes, dead);
+            process_chunk<false, false>(c, a.lo + k, w_hi, a.t_from, a.t_to, staged, pushes, dead);
         if (staged) { stage_spill<false>(c, staged); staged = 0; }
     }
 
