@@ -136,9 +136,14 @@ struct Sim {
     bool span_open = false;
     double phase_ms[kPhCount] = {0, 0, 0, 0, 0, 0};
     long long launches = 0, mover_launches = 0;
+    // mode 32 is launch-bound (2 * poisson_timestep + 7 kernels per Poisson step): its Poisson step is captured once
+    // into a CUDA graph and replayed (nothing in it depends on a value the host would have to read)
+    cudaGraphExec_t step_graph = nullptr;
+    long long graph_launches = 0, graph_mover_launches = 0;     // kernels in one replay
     void span_begin(int phase);
     void span_end();
     int collect_spans();
+    int build_step_graph();
     // optional callback after every launch of the naive scheduler (verbose state dumps, src/pic.cu:528)
     void (*naive_hook)(Sim*, void*) = nullptr;
     void* naive_hook_user = nullptr;
@@ -217,6 +222,7 @@ void Sim::release() {
     if (h_bbox_red) { cudaFreeHost(h_bbox_red); h_bbox_red = nullptr; }
     if (ev_start) { cudaEventDestroy(ev_start); ev_start = nullptr; }
     if (ev_stop) { cudaEventDestroy(ev_stop); ev_stop = nullptr; }
+    if (step_graph) { cudaGraphExecDestroy(step_graph); step_graph = nullptr; }
     if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
 }
 
@@ -341,7 +347,7 @@ int Sim::create(const picb200_config* c) {
     }
     CK(cudaStreamSynchronize(stream), "Setup");
     CK_LAST("Setup");
-    return 0;
+    return build_step_graph();
 }
 
 // What one rank tells the others (picb200_peer_export -> picb200_peer_connect): where its two local
@@ -654,14 +660,35 @@ int Sim::poisson_step(bool sync) {
         if (fused_steps(1)) return 1;
         return sync ? sync_state() : 0;
     }
-    if (op_deposit()) return 1;
-    if (op_gather()) return 1;
-    if (op_clear()) return 1;
-    if (op_mobility_begin()) return 1;
-    if (op_mobility()) return 1;
-    if (op_compact()) return 1;
-    if (op_step_end()) return 1;
+    if (step_graph && !profiling && !naive_hook) {         // mode 32: replay the captured Poisson step
+        CK(cudaGraphLaunch(step_graph, stream), "Mobility steps");
+        launches += graph_launches; mover_launches += graph_mover_launches;
+        charge_valid = true;
+        return sync ? sync_state() : 0;
+    }
+    if (op_deposit() || op_gather() || op_clear() || op_mobility_begin() || op_mobility() || op_compact() || op_step_end()) return 1;
     if (sync) return sync_state();
+    return 0;
+}
+
+// Capture one Poisson step of mode 32 into a CUDA graph (called once from create(): instantiation costs tens of
+// milliseconds the first time).  Nothing is executed and no counter is touched.
+int Sim::build_step_graph() {
+    if (cfg.mode != PICB200_MODE_NAIVE || cfg.nranks != 1 || fused || getenv("PICB200_NO_GRAPH")) return 0;
+    const long long l0 = launches, m0 = mover_launches;
+    const bool cv = charge_valid;
+    cudaGraph_t captured = nullptr;
+    CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal), "Graph capture");
+    const int rc = op_deposit() || op_gather() || op_clear() || op_mobility_begin() || op_mobility() || op_compact() || op_step_end();
+    const cudaError_t e = cudaStreamEndCapture(stream, &captured);
+    graph_launches = launches - l0; graph_mover_launches = mover_launches - m0;
+    launches = l0; mover_launches = m0; charge_valid = cv;
+    if (rc || e != cudaSuccess) { if (captured) cudaGraphDestroy(captured); return rc ? rc : fail(cudaGetErrorString(e), "Graph capture"); }
+    const cudaError_t e2 = cudaGraphInstantiate(&step_graph, captured, 0);
+    cudaGraphDestroy(captured);
+    if (e2 != cudaSuccess) { step_graph = nullptr; return fail(cudaGetErrorString(e2), "Graph capture"); }
+    CK(cudaGraphUpload(step_graph, stream), "Graph capture");
+    CK(cudaStreamSynchronize(stream), "Graph capture");
     return 0;
 }
 
