@@ -57,7 +57,7 @@ struct DevState {
     int scan_S, scan_D;     // its arguments: slots to look at, dead ones among them
     int parked;             // children of this step waiting for the compaction to make room (see FusedArgs::park)
     int error;              // 2: more children parked than the parking area holds, 3: a spilled child found no slot
-    int win_hi;             // mode 32: electrons that exist when a mobility step starts (k_freeze_window)
+    int win_lo, win_hi;     // modes 31/32: the index window of the next launch, kept on the device (k_freeze_window)
     // -- hot atomics, one 128-byte line each so they do not serialise behind one another in L2
     alignas(128) int n_alloc;                   // the reference's counter n during the mobility phase (may overshoot capacity)
     int top_alloc;                              // fused kernel: slots taken above the high-water mark; the two form ONE 64-bit
@@ -382,9 +382,15 @@ __global__ void k_compact_move(Soa s, const DevState* st, const int* __restrict_
 // Bookkeeping the reference does on the host after each phase (src/pic.cu:539-559), on the device.
 // Mode 32 (src/pic.cu:524-532) launches one kernel per mobility step over the electrons that exist when the step
 // starts; the reference reads that count back to the host before every launch, here it stays on the device.
-__global__ void k_freeze_window(DevState* st, int capacity) { st->win_hi = min(st->n_alloc, capacity); }
+// Mode 31 (src/pic.cu:514-523) relaunches over the children of the previous launch until none are born: `advance`
+// moves the window on to [old end, n); an empty window makes the launch return at once.
+__global__ void k_freeze_window(DevState* st, int capacity, int advance) {
+    if (advance) st->win_lo = st->win_hi;
+    st->win_hi = min(st->n_alloc, capacity);
+}
 __global__ void k_mobility_begin(DevState* st) {
     st->n_alloc = st->n;
+    st->win_lo = 0; st->win_hi = 0;
     st->top_alloc = st->n;
     st->n_dead = 0;
     st->n_holes = 0; st->n_movers = 0;

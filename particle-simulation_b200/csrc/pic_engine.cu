@@ -144,6 +144,8 @@ struct Sim {
     void span_end();
     int collect_spans();
     int build_step_graph();
+    // mode 31 with its generation windows kept on the device (else: the reference's host loop, src/pic.cu:514-523)
+    bool device_windows() const { return cfg.nranks == 1 && cfg.poisson_timestep <= 128 && !getenv("PICB200_HOST_SYNC"); }
     // optional callback after every launch of the naive scheduler (verbose state dumps, src/pic.cu:528)
     void (*naive_hook)(Sim*, void*) = nullptr;
     void* naive_hook_user = nullptr;
@@ -553,6 +555,16 @@ int Sim::op_mobility() {
             break;
         }
         case PICB200_MODE_CPU_SYNC: {      // src/pic.cu:514-523: relaunch over the new index range until n stops growing
+            if (device_windows()) {
+                // a child of generation g is born at step g or later: poisson_timestep + 1 passes always suffice, and
+                // the passes that find no children return at once.  No host read, the step can be replayed as a graph.
+                for (int g = 0; g <= pt; ++g) {
+                    k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity, 1);
+                    ++launches;
+                    if (launch_mover_window(-1, -1, 1, pt, false)) return 1;
+                }
+                break;
+            }
             if (sync_state()) return 1;
             int last_n = 0, n_host = std::min(h_st->n_alloc, cfg.capacity);
             while (n_host != last_n) {
@@ -567,7 +579,7 @@ int Sim::op_mobility() {
             // The reference copies n to the host before every launch; here the window of a step is frozen on the
             // device (k_freeze_window) and the host only looks when a logger wants the state.
             for (int t = 1; t <= pt; ++t) {
-                k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity);
+                k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity, 0);
                 ++launches;
                 if (launch_mover_window(0, -1, t, t, true)) return 1;
                 if (naive_hook) {
@@ -674,7 +686,7 @@ int Sim::poisson_step(bool sync) {
 // Capture one Poisson step of mode 32 into a CUDA graph (called once from create(): instantiation costs tens of
 // milliseconds the first time).  Nothing is executed and no counter is touched.
 int Sim::build_step_graph() {
-    if (cfg.mode != PICB200_MODE_NAIVE || cfg.nranks != 1 || fused || getenv("PICB200_NO_GRAPH")) return 0;
+    if (!(cfg.mode == PICB200_MODE_NAIVE || (cfg.mode == PICB200_MODE_CPU_SYNC && device_windows())) || cfg.nranks != 1 || fused || getenv("PICB200_NO_GRAPH")) return 0;
     const long long l0 = launches, m0 = mover_launches;
     const bool cv = charge_valid;
     cudaGraph_t captured = nullptr;
@@ -816,7 +828,7 @@ int picb200_run_steps(picb200_sim* sim, int32_t steps) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
     CK(cudaEventRecord(s.ev_start, s.stream), "Setup");
-    const bool host_in_loop = s.cfg.mode == PICB200_MODE_CPU_SYNC || s.cfg.nranks > 1;
+    const bool host_in_loop = (s.cfg.mode == PICB200_MODE_CPU_SYNC && !s.device_windows()) || s.cfg.nranks > 1;
     if (s.fused) {
         if (s.fused_steps(steps)) return 1;
     } else {

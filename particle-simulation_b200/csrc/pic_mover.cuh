@@ -270,6 +270,11 @@ __device__ __forceinline__ int mover_barrier_next_window(DevState* st, unsigned 
 template <bool kPersistent>
 __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    // hi < 0 / lo < 0: the window was frozen on the device by k_freeze_window (modes 31/32 without a host read per
+    // launch); an empty one ends the launch before anything is staged
+    const int w_hi = (!kPersistent && a.hi < 0) ? ld_volatile_i32(&a.st->win_hi) : a.hi;
+    const int w_lo = (!kPersistent && a.lo < 0) ? ld_volatile_i32(&a.st->win_lo) : a.lo;
+    if (!kPersistent && w_hi <= w_lo) return;
     {   // stage the collision tables (120 KB) once per CTA, 128-bit copies
         const float4* src = reinterpret_cast<const float4*>(a.tables);
         float4* dst = reinterpret_cast<float4*>(smem_raw);
@@ -321,12 +326,10 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
             lo = hi;
         }
     } else {
-        // hi < 0: the window is [0, win_hi), frozen on the device by k_freeze_window (mode 32 without a host read per step)
-        const int w_hi = a.hi < 0 ? ld_volatile_i32(&a.st->win_hi) : a.hi;
-        const int span = w_hi - a.lo;
+        const int span = w_hi - w_lo;
         const int rounded = (span + 31) & ~31;
         for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x)
-            process_chunk<false, false>(c, a.lo + k, w_hi, a.t_from, a.t_to, staged, pushes, dead);
+            process_chunk<false, false>(c, w_lo + k, w_hi, a.t_from, a.t_to, staged, pushes, dead);
         if (staged) { stage_spill<false>(c, staged); staged = 0; }
     }
 

@@ -78,7 +78,7 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
         const int t_begin = restart ? s.h_st->poisson_index : 0;
         const int P = std::max(0, cfg.poisson_steps - t_begin);     // Poisson steps still to do
         const bool verbose = say && cfg.verbose != 0;
-        const bool host_in_loop = verbose || cfg.mode == PICB200_MODE_CPU_SYNC || cfg.nranks > 1;     // (mode 32 keeps its step windows on the device)
+        const bool host_in_loop = verbose || (cfg.mode == PICB200_MODE_CPU_SYNC && !s.device_windows()) || cfg.nranks > 1;     // (mode 32 keeps its step windows on the device)
         bool failed = false;
         if (verbose && cfg.mode == PICB200_MODE_NAIVE) { s.naive_hook = naive_step_logger; s.naive_hook_user = sim; }
         if (!host_in_loop) {
