@@ -87,6 +87,7 @@ struct Sim {
     int device = 0;
     int sm_count = 0;
     int mover_threads = 1024;
+    int fused_smem_pad = 0;          // PICB200_SMEM_PAD: extra dynamic shared memory for the fused kernel (carve-out experiments)
     int blocks_per_sm = 1;
     int aux_blocks = 0;
     uint2 seed{};
@@ -320,11 +321,12 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&log, sizeof(StepLog) * (size_t)log_len), "Minor alloc");
     CK(cudaMemsetAsync(log, 0, sizeof(StepLog) * (size_t)log_len, stream), "Minor alloc");
 
+    if (const char* pad = getenv("PICB200_SMEM_PAD")) fused_smem_pad = std::max(0, std::min(atoi(pad), 227 * 1024 - 512 - kFusedSmemBytes(1024)));
     CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
     fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
@@ -622,7 +624,8 @@ int Sim::fused_steps(int steps) {
     for (int done = 0; done < steps; done += per_launch) {
         if (op_mobility_begin()) return 1;
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
-                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy};
+                    per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy,
+                    std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt))};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
@@ -637,7 +640,7 @@ int Sim::fused_steps(int steps) {
         const void* kern = peer ? (adopt ? (const void*)k_poisson_fused<true, true> : (const void*)k_poisson_fused<true, false>)
                                 : (adopt ? (const void*)k_poisson_fused<false, true> : (const void*)k_poisson_fused<false, false>);
         CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)sm_count),
-                                       dim3((unsigned)mover_threads), args, (size_t)kFusedSmemBytes(mover_threads), stream),
+                                       dim3((unsigned)mover_threads), args, (size_t)kFusedSmemBytes(mover_threads) + fused_smem_pad, stream),
            "Mobility steps");
         ++launches; ++mover_launches;
         span_end();

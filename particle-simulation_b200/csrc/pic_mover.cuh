@@ -26,17 +26,38 @@ struct MoverArgs {
     uint2 seed;
 };
 
-// Children are staged per warp in shared memory: 12 words x 32 entries, field-major, so both the
-// ranked writes and the lane-indexed reads are bank-conflict free.
+// Children are staged per warp in shared memory: 12 words x kSS entries, field-major, so both the
+// ranked writes and the lane-indexed reads are bank-conflict free.  The unfused schedulers (k_mover) use the
+// first 32 entries; the fused kernel uses all 64, so that it can wait for enough children to make up a batch
+// of 32 with similar birth steps (fused_staged) -- a batch costs poisson_timestep - min(birth step) lockstep
+// steps whatever its lanes hold.
 constexpr int kStageWords = 12;
-constexpr int kStageBytesPerWarp = kStageWords * 32 * 4;
+#ifndef PIC_KSS
+#define PIC_KSS 44
+#endif
+constexpr int kSS = PIC_KSS;          // entries per field (stride in words): tables + 32 stages + pools must stay below the
+                                      // 196 KB shared-memory carve-out -- the next one (228 KB) leaves the L1 28 KB, and the
+                                      // memory-bound configurations lose far more to that than batching wins (measured)
+constexpr int kStageBytesPerWarp = kStageWords * kSS * 4;
 constexpr int kMoverSmemBytes(int threads) { return kTableSmemBytes + (threads / 32) * kStageBytesPerWarp; }
-constexpr int kDrainThreshold = 16;   // push staged children once this many wait
+constexpr int kDrainThreshold = 16;   // k_mover: push staged children once this many wait
+constexpr int kFusedDrainAt = kSS - 20 > 16 ? kSS - 20 : 16;   // fused kernel: ... once this many wait (PICB200_DRAIN_AT); 20 entries stay free for the next chunk
 
 struct El {
     float x, y, z, vx, vy, vz, ax, ay, az;
     unsigned long long id;
 };
+
+// PIC_THR_GLOBAL (experiment): the {split, split+remove} rows (80 KB) stay in global memory and are read through
+// the L1 (ld.global.nc); the fused kernel then needs 118 KB of shared memory instead of 198 KB and the L1 grows
+// from 60 KB to 124 KB.
+#ifdef PIC_THR_GLOBAL
+constexpr int kFusedSkip = kThrBytes;
+#define PIC_THR_ROW(c, i) __ldg((c).thr + (i))
+#else
+constexpr int kFusedSkip = 0;
+#define PIC_THR_ROW(c, i) ((c).thr[(i)])
+#endif
 
 struct MoverCtx {
     Soa s;
@@ -44,6 +65,7 @@ struct MoverCtx {
     const float2* thr;
     const float* edge;
     uint32_t* stage;
+    int stage_cap;       // entries of the stage in use: 32 (k_mover) or kSS (fused kernel)
     int cap, pt, lane, stepwise;
     int adopt_min;       // fused kernel, adopting loop: dead lanes in the warp from which children are handed over
     int* pool;           // fused kernel: free slots this warp has come across in the current Poisson step (shared memory)
@@ -75,8 +97,8 @@ __device__ __forceinline__ void reserve_fused(const MoverCtx& c, int count, int 
 // A stage entry carries the parent's id and the birth step; the child's own id is derived when the
 // entry is consumed (all lanes busy) instead of when it is written (one or two lanes busy).
 __device__ __forceinline__ unsigned long long staged_child_id(const MoverCtx& c, const uint32_t* g) {
-    const unsigned long long parent = ((unsigned long long)g[11 * 32] << 32) | g[10 * 32];
-    return child_id(parent, (unsigned long long)(c.g0 + g[9 * 32]));
+    const unsigned long long parent = ((unsigned long long)g[11 * kSS] << 32) | g[10 * kSS];
+    return child_id(parent, (unsigned long long)(c.g0 + g[9 * kSS]));
 }
 
 // Write the staged children to the global store as they are (timestamp = birth step): they still
@@ -84,28 +106,35 @@ __device__ __forceinline__ unsigned long long staged_child_id(const MoverCtx& c,
 template <bool kCount>
 __device__ __forceinline__ void stage_spill(const MoverCtx& c, int count) {
     __syncwarp();
-    int vslot, slot;
+    int vbase, sbase;
     if (c.pool) {            // fused kernel: the reference's index decides whether the child exists, it lives above the mark
-        reserve_fused(c, count, count, vslot, slot);
-        vslot += c.lane; slot += c.lane;
-        if (c.lane < count && vslot < c.cap && slot >= c.cap) *(volatile int*)&c.st->error = 3;   // unfinished children cannot be parked
-        if (c.lane < count && vslot >= c.cap && slot < c.cap) __stcg(c.s.ts + slot, kDead);       // a slot above the mark nobody was born into: a hole
+        reserve_fused(c, count, count, vbase, sbase);
     } else {
-        vslot = slot = reserve_slots(c, count) + c.lane;
+        vbase = sbase = reserve_slots(c, count);
     }
-    const bool w = c.lane < count && vslot < c.cap && slot < c.cap;
-    if (w) {
-        const uint32_t* g = c.stage + c.lane;
-        __stcg(c.s.x + slot, __uint_as_float(g[0 * 32])); __stcg(c.s.y + slot, __uint_as_float(g[1 * 32])); __stcg(c.s.z + slot, __uint_as_float(g[2 * 32]));
-        __stcg(c.s.vx + slot, __uint_as_float(g[3 * 32])); __stcg(c.s.vy + slot, __uint_as_float(g[4 * 32])); __stcg(c.s.vz + slot, __uint_as_float(g[5 * 32]));
-        __stcg(c.s.ax + slot, __uint_as_float(g[6 * 32])); __stcg(c.s.ay + slot, __uint_as_float(g[7 * 32])); __stcg(c.s.az + slot, __uint_as_float(g[8 * 32]));
-        const int tb = (int)g[9 * 32];
-        __stcg(c.s.ts + slot, (c.stepwise && tb == c.pt) ? -1 : tb);
-        __stcg(c.s.id + slot, staged_child_id(c, g));
+    int written = 0;
+#pragma unroll 1
+    for (int h = 0; h < count; h += 32) {       // the fused kernel's stage holds up to kSS = 64 children
+        const int e = h + c.lane;
+        const int vslot = vbase + e, slot = sbase + e;
+        if (c.pool) {
+            if (e < count && vslot < c.cap && slot >= c.cap) *(volatile int*)&c.st->error = 3;   // unfinished children cannot be parked
+            if (e < count && vslot >= c.cap && slot < c.cap) __stcg(c.s.ts + slot, kDead);       // a slot above the mark nobody was born into: a hole
+        }
+        const bool w = e < count && vslot < c.cap && slot < c.cap;
+        if (w) {
+            const uint32_t* g = c.stage + e;
+            __stcg(c.s.x + slot, __uint_as_float(g[0 * kSS])); __stcg(c.s.y + slot, __uint_as_float(g[1 * kSS])); __stcg(c.s.z + slot, __uint_as_float(g[2 * kSS]));
+            __stcg(c.s.vx + slot, __uint_as_float(g[3 * kSS])); __stcg(c.s.vy + slot, __uint_as_float(g[4 * kSS])); __stcg(c.s.vz + slot, __uint_as_float(g[5 * kSS]));
+            __stcg(c.s.ax + slot, __uint_as_float(g[6 * kSS])); __stcg(c.s.ay + slot, __uint_as_float(g[7 * kSS])); __stcg(c.s.az + slot, __uint_as_float(g[8 * kSS]));
+            const int tb = (int)g[9 * kSS];
+            __stcg(c.s.ts + slot, (c.stepwise && tb == c.pt) ? -1 : tb);
+            __stcg(c.s.id + slot, staged_child_id(c, g));
+        }
+        if (kCount) written += __popc(__ballot_sync(kFull, w));
     }
     if (kCount) {
-        const unsigned m = __ballot_sync(kFull, w);
-        if (c.lane == 0 && m) atomicAdd(&c.st->n_unfinished, __popc(m));
+        if (c.lane == 0 && written) atomicAdd(&c.st->n_unfinished, written);
     }
     __syncwarp();
 }
@@ -147,7 +176,7 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
                 const uint32_t w = (g & 2u) ? w23 : w01;
                 const float r = __fmul_rn(uniform01(w), 100.0f);
                 const float en = __fmaf_rn(e.vz, e.vz, __fmaf_rn(e.vy, e.vy, __fmul_rn(e.vx, e.vx)));
-                const float2 th = c.thr[energy_index(en, c.edge)];
+                const float2 th = PIC_THR_ROW(c, energy_index(en, c.edge));
                 if (r < th.x) {              // ionisation: the child copies the pre-flip state
                     spawn = true;
                     cvx = e.vx; cvy = e.vy; cvz = e.vz;
@@ -160,14 +189,14 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
         const unsigned m = __ballot_sync(kFull, spawn);
         if (m) {
             const int cnt = __popc(m);
-            if (staged + cnt > 32) { stage_spill<kCountSpill>(c, staged); staged = 0; }
+            if (staged + cnt > c.stage_cap) { stage_spill<kCountSpill>(c, staged); staged = 0; }
             if (spawn) {
                 uint32_t* q = c.stage + staged + __popc(m & lanemask_lt());
-                q[0 * 32] = __float_as_uint(e.x); q[1 * 32] = __float_as_uint(e.y); q[2 * 32] = __float_as_uint(e.z);
-                q[3 * 32] = __float_as_uint(cvx); q[4 * 32] = __float_as_uint(cvy); q[5 * 32] = __float_as_uint(cvz);
-                q[6 * 32] = __float_as_uint(e.ax); q[7 * 32] = __float_as_uint(e.ay); q[8 * 32] = __float_as_uint(e.az);
-                q[9 * 32] = (uint32_t)t;
-                q[10 * 32] = (uint32_t)e.id; q[11 * 32] = (uint32_t)(e.id >> 32);
+                q[0 * kSS] = __float_as_uint(e.x); q[1 * kSS] = __float_as_uint(e.y); q[2 * kSS] = __float_as_uint(e.z);
+                q[3 * kSS] = __float_as_uint(cvx); q[4 * kSS] = __float_as_uint(cvy); q[5 * kSS] = __float_as_uint(cvz);
+                q[6 * kSS] = __float_as_uint(e.ax); q[7 * kSS] = __float_as_uint(e.ay); q[8 * kSS] = __float_as_uint(e.az);
+                q[9 * kSS] = (uint32_t)t;
+                q[10 * kSS] = (uint32_t)e.id; q[11 * kSS] = (uint32_t)(e.id >> 32);
             }
             staged += cnt;
         }
@@ -219,10 +248,10 @@ __device__ __forceinline__ void process_staged(const MoverCtx& c, int& staged, u
     int tb = 0;
     if (c.lane < k) {
         const uint32_t* g = c.stage + c.lane;
-        e.x = __uint_as_float(g[0 * 32]); e.y = __uint_as_float(g[1 * 32]); e.z = __uint_as_float(g[2 * 32]);
-        e.vx = __uint_as_float(g[3 * 32]); e.vy = __uint_as_float(g[4 * 32]); e.vz = __uint_as_float(g[5 * 32]);
-        e.ax = __uint_as_float(g[6 * 32]); e.ay = __uint_as_float(g[7 * 32]); e.az = __uint_as_float(g[8 * 32]);
-        tb = (int)g[9 * 32];
+        e.x = __uint_as_float(g[0 * kSS]); e.y = __uint_as_float(g[1 * kSS]); e.z = __uint_as_float(g[2 * kSS]);
+        e.vx = __uint_as_float(g[3 * kSS]); e.vy = __uint_as_float(g[4 * kSS]); e.vz = __uint_as_float(g[5 * kSS]);
+        e.ax = __uint_as_float(g[6 * kSS]); e.ay = __uint_as_float(g[7 * kSS]); e.az = __uint_as_float(g[8 * kSS]);
+        tb = (int)g[9 * kSS];
         e.id = staged_child_id(c, g);
     }
     staged = 0;
@@ -285,12 +314,13 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     MoverCtx c;
     c.s = a.s;
     c.st = a.st;
-    c.thr = reinterpret_cast<const float2*>(smem_raw);
+    c.thr = kFusedSkip ? reinterpret_cast<const float2*>(a.tables) : reinterpret_cast<const float2*>(smem_raw);
     c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
-    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * 32);
+    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
     c.cap = a.capacity;
     c.pt = a.pt;
     c.lane = threadIdx.x & 31;
+    c.stage_cap = 32;
     c.stepwise = a.stepwise;
     c.pool = nullptr;
     c.g0 = (unsigned)a.st->poisson_index * (unsigned)a.pt;
@@ -381,6 +411,7 @@ struct FusedArgs {
     int park_cap;
     int adopt_min;               // kAdoptMin, or PICB200_ADOPT_MIN (33: never)
     int compact_policy;          // 0: lazy (default); 1: after every Poisson step (PICB200_COMPACT=eager); 2: lazy, no capacity guard (tests)
+    int drain_at;                // staged children from which a warp pushes a batch between two chunks (kFusedDrainAt, PICB200_DRAIN_AT)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -533,7 +564,7 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
         const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
         const float r = __fmul_rn(uniform01((g & 2u) ? w23 : w01), 100.0f);
         const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
-        const float2 th = c.thr[energy_index(en, c.edge)];
+        const float2 th = PIC_THR_ROW(c, energy_index(en, c.edge));
         const bool coll = act & !oob;
         const bool spawn = coll & (r < th.x);                    // ionisation
         const bool die = act & (oob | (!spawn & (r < th.y)));    // left the domain, or attachment
@@ -568,14 +599,14 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
             const unsigned sm = kAdopt ? __ballot_sync(kFull, stage_it) : m;
             if (sm) {
                 const int cnt = __popc(sm);
-                if (staged + cnt > 32) { stage_spill<true>(c, staged); staged = 0; }
+                if (staged + cnt > c.stage_cap) { stage_spill<true>(c, staged); staged = 0; }
                 if (stage_it) {                                  // the child copies the pre-flip state
                     uint32_t* q = c.stage + staged + __popc(sm & lanemask_lt());
-                    q[0 * 32] = __float_as_uint(x); q[1 * 32] = __float_as_uint(y); q[2 * 32] = __float_as_uint(z);
-                    q[3 * 32] = __float_as_uint(vx); q[4 * 32] = __float_as_uint(vy); q[5 * 32] = __float_as_uint(vz);
-                    q[6 * 32] = __float_as_uint(ax); q[7 * 32] = __float_as_uint(ay); q[8 * 32] = __float_as_uint(az);
-                    q[9 * 32] = (uint32_t)t;
-                    q[10 * 32] = (uint32_t)id; q[11 * 32] = (uint32_t)(id >> 32);
+                    q[0 * kSS] = __float_as_uint(x); q[1 * kSS] = __float_as_uint(y); q[2 * kSS] = __float_as_uint(z);
+                    q[3 * kSS] = __float_as_uint(vx); q[4 * kSS] = __float_as_uint(vy); q[5 * kSS] = __float_as_uint(vz);
+                    q[6 * kSS] = __float_as_uint(ax); q[7 * kSS] = __float_as_uint(ay); q[8 * kSS] = __float_as_uint(az);
+                    q[9 * kSS] = (uint32_t)t;
+                    q[10 * kSS] = (uint32_t)id; q[11 * kSS] = (uint32_t)(id >> 32);
                 }
                 staged += cnt;
             }
@@ -712,21 +743,64 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
     deposit_lanes(f.B, alive, ix, iy, iz, c.lane, f.s_box);
 }
 
-// children out of the warp's stage: push, deposit, store once (see process_staged)
-__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead, int& npool) {
-    const int k = staged;
+// More than 32 children wait in the stage: bring the 32 with the EARLIEST birth steps to the end of the stage
+// (entries [k-32, k)) and close the others up at its start, keeping their order.  A batch costs
+// poisson_timestep - min(birth step) lockstep steps whatever its lanes hold, so the late-born wait for a
+// batch of their own kind.  Warp-uniform; field by field, every entry is read into a register before any is rewritten.
+__device__ __forceinline__ void stage_select_earliest(const MoverCtx& c, int k) {
+    const int lane = c.lane;
+    const bool v1 = lane + 32 < k;                           // (k > 32: entry `lane` always exists)
+    const int tb0 = (int)c.stage[9 * kSS + lane], tb1 = v1 ? (int)c.stage[9 * kSS + lane + 32] : 0x7fffffff;
+    // T = the 32nd smallest birth step: the smallest T with #(tb <= T) >= 32
+    int lo = 0, hi = c.pt;                                   // #(tb <= pt) = k >= 32
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const int cnt = __popc(__ballot_sync(kFull, tb0 <= mid)) + __popc(__ballot_sync(kFull, tb1 <= mid));
+        if (cnt >= 32) hi = mid; else lo = mid + 1;
+    }
+    const int T = lo;
+    const unsigned lt = lanemask_lt();
+    const unsigned less0 = __ballot_sync(kFull, tb0 < T), less1 = __ballot_sync(kFull, tb1 < T);
+    const unsigned eq0 = __ballot_sync(kFull, tb0 == T), eq1 = __ballot_sync(kFull, tb1 == T);
+    const int need = 32 - __popc(less0) - __popc(less1);     // entries with tb == T that still fit (>= 1)
+    const bool s0 = (tb0 < T) || (tb0 == T && __popc(eq0 & lt) < need);
+    const bool s1 = (tb1 < T) || (tb1 == T && __popc(eq0) + __popc(eq1 & lt) < need);
+    const unsigned sel0 = __ballot_sync(kFull, s0), sel1 = __ballot_sync(kFull, s1);
+    const unsigned val1 = __ballot_sync(kFull, v1);
+    const int rest = k - 32;
+    // new position: selected entries keep their order behind the others
+    const int d0 = s0 ? rest + __popc(sel0 & lt) : __popc(~sel0 & lt);
+    const int d1 = s1 ? rest + __popc(sel0) + __popc(sel1 & lt) : __popc(~sel0) + __popc(~sel1 & val1 & lt);
+    // the fields are separate arrays: permute them one at a time (two registers instead of twenty-four)
+#pragma unroll
+    for (int w = 0; w < kStageWords; ++w) {
+        uint32_t* fld = c.stage + w * kSS;
+        const uint32_t a = fld[lane], b = v1 ? fld[lane + 32] : 0u;
+        __syncwarp();
+        fld[d0] = a;
+        if (v1) fld[d1] = b;
+    }
     __syncwarp();
+}
+
+// children out of the warp's stage: push, deposit, store once (see process_staged).  At most 32 at a time:
+// of more, the earliest-born 32 (stage_select_earliest).
+__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead, int& npool) {
+    __syncwarp();
+    if (staged > 32) stage_select_earliest(c, staged);
+    const int k = min(staged, 32);
+    const int rest = staged - k;
     El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     int tb = 0;
     if (c.lane < k) {
-        const uint32_t* g = c.stage + c.lane;
-        e.x = __uint_as_float(g[0 * 32]); e.y = __uint_as_float(g[1 * 32]); e.z = __uint_as_float(g[2 * 32]);
-        e.vx = __uint_as_float(g[3 * 32]); e.vy = __uint_as_float(g[4 * 32]); e.vz = __uint_as_float(g[5 * 32]);
-        e.ax = __uint_as_float(g[6 * 32]); e.ay = __uint_as_float(g[7 * 32]); e.az = __uint_as_float(g[8 * 32]);
-        tb = (int)g[9 * 32];
+        const uint32_t* g = c.stage + rest + c.lane;
+        e.x = __uint_as_float(g[0 * kSS]); e.y = __uint_as_float(g[1 * kSS]); e.z = __uint_as_float(g[2 * kSS]);
+        e.vx = __uint_as_float(g[3 * kSS]); e.vy = __uint_as_float(g[4 * kSS]); e.vz = __uint_as_float(g[5 * kSS]);
+        e.ax = __uint_as_float(g[6 * kSS]); e.ay = __uint_as_float(g[7 * kSS]); e.az = __uint_as_float(g[8 * kSS]);
+        tb = (int)g[9 * kSS];
         e.id = staged_child_id(c, g);
     }
-    staged = 0;
+    staged = rest;                                           // grandchildren are appended behind the children that still wait
     __syncwarp();
     // the first p children move into free slots this warp holds, the others go above the high-water mark
     const int p = min(k, npool);
@@ -773,7 +847,12 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
 
 constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
-constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPushStageBytesPerWarp + kPoolSlots * 4); }
+// per warp: the children stage (whose first bytes double as the peer exchange's row buffer: that runs between
+// barrier 1 and barrier 2, when every stage is empty) and the free-slot pool
+static_assert(kPushStageBytesPerWarp <= kStageBytesPerWarp, "the peer row buffer lives inside the children stage");
+constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes - kFusedSkip + (threads / 32) * (kStageBytesPerWarp + kPoolSlots * 4); }
+static_assert(kFusedSmemBytes(1024) + 1024 <= 227 * 1024, "shared memory of the fused kernel");
+static_assert(kSS >= 32 && kSS <= 64, "stage_select_earliest handles up to 64 entries");
 
 // kAdopt: the chunks use the adopting step loop (lockstep_push); the host picks it for poisson_timestep >= kAdoptMinSteps --
 // it carries more state through every step and only pays when lanes die out long before the Poisson step ends.
@@ -789,7 +868,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     {
         const float4* src = reinterpret_cast<const float4*>(a.tables);
         float4* dst = reinterpret_cast<float4*>(smem_raw);
-        for (int k = threadIdx.x; k < kAllTableBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
+        for (int k = kFusedSkip / 16 + threadIdx.x; k < kAllTableBytes / 16; k += blockDim.x) dst[k - kFusedSkip / 16] = __ldg(src + k);
     }
     if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
     __syncthreads();
@@ -798,17 +877,19 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     MoverCtx c;
     c.s = a.s;
     c.st = st;
-    c.thr = reinterpret_cast<const float2*>(smem_raw);
-    c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
-    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kAllTableBytes) + (threadIdx.x >> 5) * (kStageWords * 32);
+    unsigned char* const smem_t = smem_raw - kFusedSkip;      // image offsets -> shared memory
+    c.thr = kFusedSkip ? reinterpret_cast<const float2*>(a.tables) : reinterpret_cast<const float2*>(smem_raw);
+    c.edge = reinterpret_cast<const float*>(smem_t + kThrBytes);
+    c.stage = reinterpret_cast<uint32_t*>(smem_t + kAllTableBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
     c.cap = a.capacity;
     c.pt = a.pt;
     c.lane = threadIdx.x & 31;
+    c.stage_cap = kSS;
     c.stepwise = 0;
     c.adopt_min = a.adopt_min;
     c.seed = a.seed;
     FusedCtx f;
-    f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
+    f.bnd = reinterpret_cast<const float*>(smem_t + kTableSmemBytes);
     f.s_box = s_box;
     f.efc = a.efc;
     f.park = a.park;
@@ -817,8 +898,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     unsigned seq = 0;
     const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
     unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
-    int* const push_stage = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPushSegCells;
-    c.pool = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * (kStageBytesPerWarp + kPushStageBytesPerWarp)) + (threadIdx.x >> 5) * kPoolSlots;
+    int* const push_stage = reinterpret_cast<int*>(c.stage);        // peer exchange only, while the stage is empty
+    c.pool = reinterpret_cast<int*>(smem_t + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPoolSlots;
     volatile DevState* const v = st;
 
     // ---- what ONE thread per block fetches after each grid barrier (BlockBc): every thread asking L2 for
@@ -939,7 +1020,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 more = chunk < chunks;
                 if (more) fused_chunk_fast<kAdopt>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
             }
-            if (staged >= kDrainThreshold || (!more && staged)) fused_staged(c, f, staged, pushes, dead, npool);
+            if (staged >= a.drain_at || (!more && staged)) fused_staged(c, f, staged, pushes, dead, npool);
         }
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
@@ -993,7 +1074,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             const int rounded = (hi - lo + 31) & ~31;
             for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x) {
                 fused_chunk<true>(c, f, lo + k, hi, staged, pushes, dead);
-                if (staged >= kDrainThreshold) fused_staged(c, f, staged, pushes, dead, npool);
+                if (staged >= a.drain_at) fused_staged(c, f, staged, pushes, dead, npool);
             }
             while (staged) fused_staged(c, f, staged, pushes, dead, npool);
             lo = hi;

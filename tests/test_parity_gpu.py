@@ -341,6 +341,37 @@ def test_lazy_compaction_equals_compaction_every_step(engine, oracle, split, rem
     assert lazy[:4] == (c["n"], c["added"], c["removed"], c["pushes"])
 
 
+@pytest.mark.parametrize("drain_at", [1, 16, 33, 40, 64])
+@pytest.mark.parametrize("pt,split,remove", [(10, 1.8, 1.8), (10, 6.0, 5.0), (7, 12.0, 14.0)])
+def test_children_batching_policy_matches_oracle(engine, oracle, drain_at, pt, split, remove):
+    """The fused kernel lets children wait in the warp's 64-entry stage and pushes them 32 at a time, earliest-born
+    first (stage_select_earliest); PICB200_DRAIN_AT moves the point at which a warp stops to push a batch, from
+    "at once" (1) to "only when the stage is full or the chunks are gone" (64: the stage overflows and spills in
+    the heavy tables).  Whatever the batches, the electrons are those of the oracle, bit for bit."""
+    rows = np.tile(np.array([[split, remove]], dtype=np.float32), (10000, 1))
+    n = 640000                                   # ~4 chunks per warp of a 148-SM grid: the stages fill up across chunks
+    pos, vel = hot_state(n, seed=33)
+    old = os.environ.get("PICB200_DRAIN_AT")
+    os.environ["PICB200_DRAIN_AT"] = str(drain_at)
+    try:
+        with engine.Sim(capacity=4 * n, poisson_timestep=pt, mode=0, table_rows=rows, poisson_steps=3) as sim:
+            sim.upload(*pos, *vel)
+            sim.run_steps(3)
+            m, d = sim.summary(), sim.download()
+    finally:
+        if old is None:
+            os.environ.pop("PICB200_DRAIN_AT", None)
+        else:
+            os.environ["PICB200_DRAIN_AT"] = old
+    o = oracle.Oracle(capacity=4 * n, poisson_timestep=pt, table_rows=rows)
+    o.upload(*pos, *vel)
+    o.run(3)
+    c = o.counters()
+    assert (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"])
+    assert m["total_added"] > n // 4
+    assert_state_equal(d, o.download_sorted())
+
+
 def test_lazy_compaction_parks_children_near_capacity(engine, oracle):
     """Holes in place shift the slots of new children upwards; a child whose shifted slot passes the capacity
     while the reference's counter does not is parked and placed by the compaction the step then ends with.
