@@ -48,17 +48,6 @@ struct El {
     unsigned long long id;
 };
 
-// PIC_THR_GLOBAL (experiment): the {split, split+remove} rows (80 KB) stay in global memory and are read through
-// the L1 (ld.global.nc); the fused kernel then needs 118 KB of shared memory instead of 198 KB and the L1 grows
-// from 60 KB to 124 KB.
-#ifdef PIC_THR_GLOBAL
-constexpr int kFusedSkip = kThrBytes;
-#define PIC_THR_ROW(c, i) __ldg((c).thr + (i))
-#else
-constexpr int kFusedSkip = 0;
-#define PIC_THR_ROW(c, i) ((c).thr[(i)])
-#endif
-
 struct MoverCtx {
     Soa s;
     DevState* st;
@@ -176,7 +165,7 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
                 const uint32_t w = (g & 2u) ? w23 : w01;
                 const float r = __fmul_rn(uniform01(w), 100.0f);
                 const float en = __fmaf_rn(e.vz, e.vz, __fmaf_rn(e.vy, e.vy, __fmul_rn(e.vx, e.vx)));
-                const float2 th = PIC_THR_ROW(c, energy_index(en, c.edge));
+                const float2 th = c.thr[energy_index(en, c.edge)];
                 if (r < th.x) {              // ionisation: the child copies the pre-flip state
                     spawn = true;
                     cvx = e.vx; cvy = e.vy; cvz = e.vz;
@@ -314,7 +303,7 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     MoverCtx c;
     c.s = a.s;
     c.st = a.st;
-    c.thr = kFusedSkip ? reinterpret_cast<const float2*>(a.tables) : reinterpret_cast<const float2*>(smem_raw);
+    c.thr = reinterpret_cast<const float2*>(smem_raw);
     c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
     c.stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
     c.cap = a.capacity;
@@ -564,7 +553,7 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
         const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
         const float r = __fmul_rn(uniform01((g & 2u) ? w23 : w01), 100.0f);
         const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
-        const float2 th = PIC_THR_ROW(c, energy_index(en, c.edge));
+        const float2 th = c.thr[energy_index(en, c.edge)];
         const bool coll = act & !oob;
         const bool spawn = coll & (r < th.x);                    // ionisation
         const bool die = act & (oob | (!spawn & (r < th.y)));    // left the domain, or attachment
@@ -850,7 +839,7 @@ constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
 // per warp: the children stage (whose first bytes double as the peer exchange's row buffer: that runs between
 // barrier 1 and barrier 2, when every stage is empty) and the free-slot pool
 static_assert(kPushStageBytesPerWarp <= kStageBytesPerWarp, "the peer row buffer lives inside the children stage");
-constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes - kFusedSkip + (threads / 32) * (kStageBytesPerWarp + kPoolSlots * 4); }
+constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPoolSlots * 4); }
 static_assert(kFusedSmemBytes(1024) + 1024 <= 227 * 1024, "shared memory of the fused kernel");
 static_assert(kSS >= 32 && kSS <= 64, "stage_select_earliest handles up to 64 entries");
 
@@ -868,7 +857,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     {
         const float4* src = reinterpret_cast<const float4*>(a.tables);
         float4* dst = reinterpret_cast<float4*>(smem_raw);
-        for (int k = kFusedSkip / 16 + threadIdx.x; k < kAllTableBytes / 16; k += blockDim.x) dst[k - kFusedSkip / 16] = __ldg(src + k);
+        for (int k = threadIdx.x; k < kAllTableBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
     }
     if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
     __syncthreads();
@@ -877,10 +866,9 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     MoverCtx c;
     c.s = a.s;
     c.st = st;
-    unsigned char* const smem_t = smem_raw - kFusedSkip;      // image offsets -> shared memory
-    c.thr = kFusedSkip ? reinterpret_cast<const float2*>(a.tables) : reinterpret_cast<const float2*>(smem_raw);
-    c.edge = reinterpret_cast<const float*>(smem_t + kThrBytes);
-    c.stage = reinterpret_cast<uint32_t*>(smem_t + kAllTableBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
+    c.thr = reinterpret_cast<const float2*>(smem_raw);
+    c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
+    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kAllTableBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
     c.cap = a.capacity;
     c.pt = a.pt;
     c.lane = threadIdx.x & 31;
@@ -889,7 +877,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     c.adopt_min = a.adopt_min;
     c.seed = a.seed;
     FusedCtx f;
-    f.bnd = reinterpret_cast<const float*>(smem_t + kTableSmemBytes);
+    f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
     f.s_box = s_box;
     f.efc = a.efc;
     f.park = a.park;
@@ -899,7 +887,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
     unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
     int* const push_stage = reinterpret_cast<int*>(c.stage);        // peer exchange only, while the stage is empty
-    c.pool = reinterpret_cast<int*>(smem_t + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPoolSlots;
+    c.pool = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPoolSlots;
     volatile DevState* const v = st;
 
     // ---- what ONE thread per block fetches after each grid barrier (BlockBc): every thread asking L2 for
