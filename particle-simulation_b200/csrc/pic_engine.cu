@@ -99,6 +99,8 @@ struct Sim {
     int park_cap = 0;
     int compact_policy = 0;
     void* soa_base = nullptr;
+    float4* field = nullptr;             // fused kernel, one rank: dense per-cell field for dense plasmas (field_rows), 2 GiB
+    int field_ratio = 2;                 // electrons per cell of the occupied box from which it is used (PICB200_FIELD_RATIO; < 0: never)
     int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
@@ -214,6 +216,7 @@ void Sim::release() {
     cudaFree(soa_base); soa_base = nullptr;
     cudaFree(park_base); park_base = nullptr;
     for (int g = 0; g < kGrids; ++g) { cudaFree(grid[g]); grid[g] = nullptr; }
+    cudaFree(field); field = nullptr;
     cudaFree(holes); holes = nullptr;
     cudaFree(movers); movers = nullptr;
     cudaFree(tables); tables = nullptr;
@@ -328,6 +331,9 @@ int Sim::create(const picb200_config* c) {
     CK(cudaFuncSetAttribute(k_poisson_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
     CK(cudaFuncSetAttribute(k_poisson_fused<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
     fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
+    if (const char* fr = getenv("PICB200_FIELD_RATIO")) field_ratio = atoi(fr);
+    if (fused && cfg.nranks == 1 && field_ratio >= 0)        // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
+        CK(cudaMalloc(&field, (size_t)kGrid * kGrid * kGrid * sizeof(float4)), "Grid alloc");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
     if (cfg.nranks > 1) {
@@ -625,7 +631,8 @@ int Sim::fused_steps(int steps) {
         if (op_mobility_begin()) return 1;
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy,
-                    std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt))};
+                    std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt)),
+                    field, field_ratio};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");

@@ -401,6 +401,8 @@ struct FusedArgs {
     int adopt_min;               // kAdoptMin, or PICB200_ADOPT_MIN (33: never)
     int compact_policy;          // 0: lazy (default); 1: after every Poisson step (PICB200_COMPACT=eager); 2: lazy, no capacity guard (tests)
     int drain_at;                // staged children from which a warp pushes a batch between two chunks (kFusedDrainAt, PICB200_DRAIN_AT)
+    float4* field;               // dense 512^3 per-cell field (field_rows), or nullptr
+    int field_ratio;             // a Poisson step computes the field per cell when n >= field_ratio * cells of the occupied box (< 0: never)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -483,10 +485,13 @@ struct BlockBc {
     int H;                          // after barrier 2
     int box_old[6];                 // box of the grid this step empties (lo xyz, hi xyz)
     int box_new[6];                 // peer mode: box of this step's own (local) deposit
+    int box_cur[6];                 // box of the grid this step gathers from
+    int use_field;                  // this step gathers from the per-cell field (field_rows)
 };
 
 struct FusedCtx {
     const float* bnd;
+    const float4* F;  // per-cell field of this Poisson step (field_rows), or nullptr: difference the counts per electron
     int* A;
     int* B;
     int* s_box;
@@ -499,14 +504,43 @@ struct FusedCtx {
 
 // updateGrid + gridToParticles for one electron's own cell (src/grid_operations.cu:29-72):
 // acc = float(EFC * double(c+ - c-)), absent neighbours at the domain faces count 0.
-__device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, int iz, float& ax, float& ay, float& az) {
-    const int* q = f.A + cell_index(ix, iy, iz);
+__device__ __forceinline__ void gather_field_direct(const int* __restrict__ A, double efc, int ix, int iy, int iz, float& ax, float& ay, float& az) {
+    const int* q = A + cell_index(ix, iy, iz);
     const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
     const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
     const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
-    ax = __double2float_rn(__dmul_rn(f.efc, (double)(xp - xm)));
-    ay = __double2float_rn(__dmul_rn(f.efc, (double)(yp - ym)));
-    az = __double2float_rn(__dmul_rn(f.efc, (double)(zp - zm)));
+    ax = __double2float_rn(__dmul_rn(efc, (double)(xp - xm)));
+    ay = __double2float_rn(__dmul_rn(efc, (double)(yp - ym)));
+    az = __double2float_rn(__dmul_rn(efc, (double)(zp - zm)));
+}
+// Dense plasmas (many electrons per cell): six scattered 32-byte sectors per electron make the L1 -> L2 request
+// path the limit of the step (ncu, cfg5 poisson_timestep = 1: l1tex2xbar 81 % busy, 84 % of the load sectors are
+// these).  The field is then computed once per CELL of the occupied box -- updateGrid as the reference runs it
+// (src/grid_operations.cu:29-56), coalesced row reads, one 16-byte record per cell -- and an electron
+// fetches ONE sector.  Same expression, same bits.  Costs one grid barrier per Poisson step, so the host switches
+// it on by density (FusedArgs::field_ratio).
+__device__ __forceinline__ void field_rows(float4* __restrict__ F, const int* __restrict__ A, const int* box /* lo xyz, hi xyz */,
+                                           double efc, int gw, int nw, int lane) {
+    const int lx = box[0], ly = box[1], lz = box[2];
+    const int wx = box[3] - lx + 1, wy = box[4] - ly + 1, wz = box[5] - lz + 1;
+    if (wx <= 0 || wy <= 0 || wz <= 0) return;
+    const int rows = wy * wz;
+    for (int r = gw; r < rows; r += nw) {
+        const int iy = ly + r % wy, iz = lz + r / wy;
+        for (int xx = lane; xx < wx; xx += 32) {
+            float ax, ay, az;
+            gather_field_direct(A, efc, lx + xx, iy, iz, ax, ay, az);
+            __stcg(F + cell_index(lx + xx, iy, iz), make_float4(ax, ay, az, 0.f));
+        }
+    }
+}
+__device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, int iz, float& ax, float& ay, float& az) {
+    if (f.F) {                                               // uniform over the grid
+        const float4 v = __ldcg(f.F + cell_index(ix, iy, iz));
+        ax = v.x; ay = v.y; az = v.z;
+    } else {
+        gather_field_direct(f.A, f.efc, ix, iy, iz, ax, ay, az);
+    }
 }
 
 // generation-0 chunk of the fused kernel: gather from A, push, deposit into B
@@ -903,6 +937,12 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         for (int k = 0; k < 6; ++k) s_box[k] = k < 3 ? kGrid : -1;
         const int old = kPeer ? (int)(e_done & 1u) : (bc.cur + 2) % kRot;
         load_box(bc.box_old, v->bbox_lo[old], v->bbox_hi[old]);
+        bc.use_field = 0;
+        if (!kPeer && a.field && a.field_ratio >= 0) {       // the same words in every block: the same decision
+            load_box(bc.box_cur, v->bbox_lo[bc.cur], v->bbox_hi[bc.cur]);
+            const long long cells = (long long)max(0, bc.box_cur[3] - bc.box_cur[0] + 1) * max(0, bc.box_cur[4] - bc.box_cur[1] + 1) * max(0, bc.box_cur[5] - bc.box_cur[2] + 1);
+            bc.use_field = (cells > 0 && (long long)bc.n >= (long long)a.field_ratio * cells) ? 1 : 0;
+        }
     };
     auto fetch_after_b1 = [&](int nxt) {
         bc.gen_hi = v->gen_hi;
@@ -980,6 +1020,12 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         const int old = kPeer ? (int)(xe & 1u) : (cur + 2) % kRot;
         f.A = a.grid[kPeer ? old : cur];   // gathered from
         f.B = a.grid[nxt];                 // (local) deposit of the next step
+        f.F = nullptr;
+        if (!kPeer && bc.use_field) {      // dense plasma: updateGrid over the occupied box first (uniform over the grid)
+            field_rows(a.field, f.A, bc.box_cur, a.efc, gwarp, nwarp, c.lane);
+            grid_barrier(st, seq, []() {});
+            f.F = a.field;
+        }
         int* const g_old = a.grid[old];
         // g_old: single GPU: gathered from one step ago, emptied during this step's main phase;
         //        peer mode: the grid gathered from in THIS step, emptied once its gathers are done (barrier 1),

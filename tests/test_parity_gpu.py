@@ -372,6 +372,39 @@ def test_children_batching_policy_matches_oracle(engine, oracle, drain_at, pt, s
     assert_state_equal(d, o.download_sorted())
 
 
+@pytest.mark.parametrize("ratio", [-1, 0, 1, 16])
+@pytest.mark.parametrize("pt", [1, 10])
+def test_per_cell_field_path_matches_oracle(engine, oracle, ratio, pt):
+    """Dense plasmas: the fused kernel computes the field once per cell of the occupied box (field_rows, the
+    reference's updateGrid, src/grid_operations.cu:29-56) and every electron fetches one record, instead of
+    differencing six counts per electron.  PICB200_FIELD_RATIO (read at create) moves the density from which it
+    does: -1 never, 0 always, 1 and 16 electrons per cell (the population below has ~3).  Same bits."""
+    rows = np.tile(np.array([[3.0, 1.0]], dtype=np.float32), (10000, 1))
+    rng = np.random.default_rng(77)
+    n = 300000
+    pos = rng.uniform(2.4, 2.86, size=(3, n)).astype(np.float32)        # 46^3 cells: ~3 electrons per cell
+    vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)
+    old = os.environ.get("PICB200_FIELD_RATIO")
+    os.environ["PICB200_FIELD_RATIO"] = str(ratio)
+    try:
+        with engine.Sim(capacity=8 * n, poisson_timestep=pt, mode=0, table_rows=rows, poisson_steps=5) as sim:
+            sim.upload(*pos, *vel)
+            sim.run_steps(2)
+            sim.run_steps(3)
+            m, d = sim.summary(), sim.download()
+    finally:
+        if old is None:
+            os.environ.pop("PICB200_FIELD_RATIO", None)
+        else:
+            os.environ["PICB200_FIELD_RATIO"] = old
+    o = oracle.Oracle(capacity=8 * n, poisson_timestep=pt, table_rows=rows)
+    o.upload(*pos, *vel)
+    o.run(5)
+    c = o.counters()
+    assert (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"])
+    assert_state_equal(d, o.download_sorted())
+
+
 def test_lazy_compaction_parks_children_near_capacity(engine, oracle):
     """Holes in place shift the slots of new children upwards; a child whose shifted slot passes the capacity
     while the reference's counter does not is parked and placed by the compaction the step then ends with.
