@@ -808,23 +808,16 @@ __device__ __forceinline__ void stage_select_earliest(const MoverCtx& c, int k) 
 
 // children out of the warp's stage: push, deposit, store once (see process_staged).  At most 32 at a time:
 // of more, the earliest-born 32 (stage_select_earliest).
-__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead, int& npool) {
-    __syncwarp();
-    if (staged > 32) stage_select_earliest(c, staged);
-    const int k = min(staged, 32);
-    const int rest = staged - k;
-    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    int tb = 0;
-    if (c.lane < k) {
-        const uint32_t* g = c.stage + rest + c.lane;
-        e.x = __uint_as_float(g[0 * kSS]); e.y = __uint_as_float(g[1 * kSS]); e.z = __uint_as_float(g[2 * kSS]);
-        e.vx = __uint_as_float(g[3 * kSS]); e.vy = __uint_as_float(g[4 * kSS]); e.vz = __uint_as_float(g[5 * kSS]);
-        e.ax = __uint_as_float(g[6 * kSS]); e.ay = __uint_as_float(g[7 * kSS]); e.az = __uint_as_float(g[8 * kSS]);
-        tb = (int)g[9 * kSS];
-        e.id = staged_child_id(c, g);
-    }
-    staged = rest;                                           // grandchildren are appended behind the children that still wait
-    __syncwarp();
+__device__ __forceinline__ void load_stage_entry(const MoverCtx& c, const uint32_t* g, El& e, int& tb) {
+    e.x = __uint_as_float(g[0 * kSS]); e.y = __uint_as_float(g[1 * kSS]); e.z = __uint_as_float(g[2 * kSS]);
+    e.vx = __uint_as_float(g[3 * kSS]); e.vy = __uint_as_float(g[4 * kSS]); e.vz = __uint_as_float(g[5 * kSS]);
+    e.ax = __uint_as_float(g[6 * kSS]); e.ay = __uint_as_float(g[7 * kSS]); e.az = __uint_as_float(g[8 * kSS]);
+    tb = (int)g[9 * kSS];
+    e.id = staged_child_id(c, g);
+}
+
+// k children in registers (lane < k: electron e, born at step tb): slots, remaining pushes, one store, deposit
+__device__ __forceinline__ void fused_batch(const MoverCtx& c, const FusedCtx& f, El& e, int tb, int k, int& staged, unsigned& pushes, int& dead, int& npool) {
     // the first p children move into free slots this warp holds, the others go above the high-water mark
     const int p = min(k, npool);
     int vslot, tbase;
@@ -866,6 +859,24 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
         __stcg(c.s.id + slot, e.id);
     }
     deposit_lanes(f.B, alive, cell_of_fast(e.x, f.bnd), cell_of_fast(e.y, f.bnd), cell_of_fast(e.z, f.bnd), c.lane, f.s_box);
+}
+
+// the warp's own stage: up to 32 children into registers (of more, the 32 earliest-born); returns their number
+__device__ __forceinline__ int staged_load(const MoverCtx& c, int& staged, El& e, int& tb) {
+    __syncwarp();
+    if (staged > 32) stage_select_earliest(c, staged);
+    const int k = min(staged, 32);
+    const int rest = staged - k;
+    if (c.lane < k) load_stage_entry(c, c.stage + rest + c.lane, e, tb);
+    staged = rest;                                           // grandchildren are appended behind the children that still wait
+    __syncwarp();
+    return k;
+}
+__device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead, int& npool) {
+    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int tb = 0;
+    const int k = staged_load(c, staged, e, tb);
+    fused_batch(c, f, e, tb, k, staged, pushes, dead, npool);
 }
 
 constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
@@ -1106,11 +1117,12 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             const int hi = bc.gen_hi;
             if (hi < 0) break;
             const int rounded = (hi - lo + 31) & ~31;
-            for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x) {
-                fused_chunk<true>(c, f, lo + k, hi, staged, pushes, dead);
-                if (staged >= a.drain_at) fused_staged(c, f, staged, pushes, dead, npool);
+            for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31;;) {         // (one call site of fused_staged)
+                const bool have = k < rounded;
+                if (have) { fused_chunk<true>(c, f, lo + k, hi, staged, pushes, dead); k += gridDim.x * blockDim.x; }
+                if (staged >= a.drain_at || (!have && staged)) fused_staged(c, f, staged, pushes, dead, npool);
+                if (!have && !staged) break;
             }
-            while (staged) fused_staged(c, f, staged, pushes, dead, npool);
             lo = hi;
         }
         PIC_TRACE(3);          // barrier 1 passed: every push of this step is done
