@@ -126,6 +126,8 @@ lib.picb200_host_energy_edges.restype = None
 lib.picb200_host_energy_edges.argtypes = [_fp]
 lib.picb200_host_cell_bounds.restype = None
 lib.picb200_host_cell_bounds.argtypes = [_fp]
+lib.picb200_host_draw_threshold.restype = C.c_float
+lib.picb200_host_draw_threshold.argtypes = [C.c_float]
 
 
 class EngineError(RuntimeError):
@@ -402,6 +404,11 @@ def read_state(path):
     out["id"] = np.frombuffer(raw, dtype="<u8", count=n, offset=off)
     assert off + 8 * n == len(raw)
     return {k: (hdr[k].item() if k != "magic" else hdr[k]) for k in hdr.dtype.names}, out
+
+
+def host_draw_threshold(chance):
+    """Threshold T on float(w) with (float(w) < T) == (r(w) < chance) for the collider's draw r (draw_threshold, pic_engine.cu)."""
+    return np.float32(lib.picb200_host_draw_threshold(C.c_float(float(chance))))
 
 
 def host_cell_bounds():

@@ -22,8 +22,8 @@ constexpr int kRot = 3;
 constexpr unsigned kFull = 0xffffffffu;
 constexpr uint32_t kTagCollide = 0u, kTagInit = 1u;
 
-// Shared-memory image of the collision tables: kRows x {split, split+remove} then
-// kRows+1 bin-edge energies (see build_energy_edges() in pic_engine.cu).
+// Shared-memory image of the collision tables: kRows x {T(split), T(split+remove)} -- the chances as thresholds on
+// float(Philox word), draw_threshold() in pic_engine.cu -- then kRows+1 bin-edge energies (build_energy_edges()).
 constexpr int kThrBytes = kRows * 8;
 constexpr int kEdgeBytes = (kRows + 1) * 4;
 constexpr int kTableSmemBytes = ((kThrBytes + kEdgeBytes + 15) / 16) * 16;

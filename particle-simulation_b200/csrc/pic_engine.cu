@@ -69,6 +69,27 @@ static void build_energy_edges(float* edge) {
 
 // bnd[k] (1 <= k < kGrid) = smallest fp32 coordinate whose cell index int(double(x)/1e-2)
 // (src/grid_operations.cu:21-23) is >= k; bnd[0] = -inf, bnd[kGrid] = +inf.
+// The collider draws r = fmul(fma(float(w), 2^-32, 2^-33), 100) from a Philox word w and tests `r < chance`
+// (src/particle_move.cu:61-79, src/random.cu:7-12).  r never decreases as float(w) grows, so the test is
+// `float(w) < T(chance)` with T the smallest fp32 in [0, 2^32] whose r is not below the chance (0: never, also for a
+// NaN chance; +inf: always).  The tables hold T, which saves the kernels an FMA and a multiply per push; equality
+// with the literal form is checked over every value float(w) can take (tests/test_table.py).
+static float draw_threshold(float chance) {
+    auto r_of = [](float f) { return std::fmaf(f, 0x1p-32f, 0x1p-33f) * 100.0f; };
+    if (!(r_of(0.0f) < chance)) return 0.0f;
+    if (r_of(4294967296.0f) < chance) return INFINITY;
+    uint32_t lo = 0u, hi = 0x4f800000u;          // bit patterns of 0.0f (r < chance) and 2^32 (not); non-negative floats order like their bits
+    while (hi - lo > 1u) {
+        const uint32_t mid = lo + (hi - lo) / 2u;
+        float f;
+        memcpy(&f, &mid, 4);
+        if (r_of(f) < chance) lo = mid; else hi = mid;
+    }
+    float t;
+    memcpy(&t, &hi, 4);
+    return t;
+}
+
 static void build_cell_bounds(float* bnd) {
     bnd[0] = -std::numeric_limits<float>::infinity();
     for (int k = 1; k < kGrid; ++k) {
@@ -271,8 +292,8 @@ int Sim::create(const picb200_config* c) {
     float* thr = reinterpret_cast<float*>(img.data());
     build_cell_bounds(reinterpret_cast<float*>(img.data() + kTableSmemBytes));
     for (int i = 0; i < kRows; ++i) {
-        thr[2 * i] = rows2[2 * (size_t)i];                                   // split_chance
-        thr[2 * i + 1] = rows2[2 * (size_t)i + 1] + rows2[2 * (size_t)i];    // remove_chance + split_chance, fp32 (src/particle_move.cu:76)
+        thr[2 * i] = draw_threshold(rows2[2 * (size_t)i]);                                   // r < split_chance
+        thr[2 * i + 1] = draw_threshold(rows2[2 * (size_t)i + 1] + rows2[2 * (size_t)i]);    // r < remove_chance + split_chance, summed in fp32 (src/particle_move.cu:76)
     }
     build_energy_edges(reinterpret_cast<float*>(img.data() + kThrBytes));
     CK(cudaMalloc(&tables, (size_t)kAllTableBytes), "CS Alloc");
@@ -1003,6 +1024,8 @@ int picb200_load_table(const char* path, float* rows2) {
 }
 // host-side copy of the edge table, for the exhaustive CPU check of the device formula
 void picb200_host_energy_edges(float* out_edges) { build_energy_edges(out_edges); }
+// the collider's threshold on float(w) for one chance (draw_threshold)
+float picb200_host_draw_threshold(float chance) { return draw_threshold(chance); }
 // likewise the 513 cell-boundary coordinates cell_of_fast() probes
 void picb200_host_cell_bounds(float* out_bounds) { build_cell_bounds(out_bounds); }
 

@@ -163,7 +163,7 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
                 }
                 const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
                 const uint32_t w = (g & 2u) ? w23 : w01;
-                const float r = __fmul_rn(uniform01(w), 100.0f);
+                const float r = __uint2float_rn(w);          // the rows hold thresholds on float(w): draw_threshold() on the host
                 const float en = __fmaf_rn(e.vz, e.vz, __fmaf_rn(e.vy, e.vy, __fmul_rn(e.vx, e.vx)));
                 const float2 th = c.thr[energy_index(en, c.edge)];
                 if (r < th.x) {              // ionisation: the child copies the pre-flip state
@@ -585,7 +585,7 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
         const bool oob = (x < 0.f) | (x >= sim) | (y < 0.f) | (y >= sim) | (z < 0.f) | (z >= sim);
         // collider, src/particle_move.cu:55-80
         const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
-        const float r = __fmul_rn(uniform01((g & 2u) ? w23 : w01), 100.0f);
+        const float r = __uint2float_rn((g & 2u) ? w23 : w01);   // the rows hold thresholds on float(w): draw_threshold() on the host
         const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
         const float2 th = c.thr[energy_index(en, c.edge)];
         const bool coll = act & !oob;
