@@ -72,12 +72,14 @@ def test_device_energy_index_formula_emulated_on_cpu(engine, tmp_path):
     assert b"mismatches 0" in r.stdout
 
 
-def test_device_cell_index_formula_emulated_on_cpu(engine, tmp_path):
+@pytest.mark.parametrize("variant", [[], ["-DONE_PROBE"]])
+def test_device_cell_index_formula_emulated_on_cpu(engine, tmp_path, variant):
     """cell_of_fast() (one fp32 multiply + a probe of exact cell boundaries) equals the reference's
-    int(double(pos)/1e-2) (src/grid_operations.cu:21-23) for EVERY fp32 with |x| <= 8 (2.2e9 values)."""
+    int(double(pos)/1e-2) (src/grid_operations.cu:21-23) for EVERY fp32 with |x| <= 8 (2.2e9 values);
+    -DONE_PROBE: the single-probe form prepared behind PIC_CELL_ONE_PROBE."""
     exe = tmp_path / "cci"
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    subprocess.run([cxx, "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fopenmp", "-o", str(exe),
+    subprocess.run([cxx, "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fopenmp", *variant, "-o", str(exe),
                     os.path.join(ROOT, "tests", "tools", "check_cell_index.cpp")], check=True)
     r = subprocess.run([str(exe)], input=engine.host_cell_bounds().tobytes(), capture_output=True)
     assert r.returncode == 0, r.stderr.decode()[:2000]
