@@ -107,6 +107,10 @@ void        picb200_config_default(picb200_config* cfg);
  * electrons_out may be NULL; otherwise it receives min(final_n, electrons_cap) records in slot order. */
 int picb200_run(const picb200_config* cfg, picb200_summary* out,
                 picb200_electron* electrons_out, int64_t electrons_cap);
+/* The same run, but the simulation is handed back alive (*sim_out; release with picb200_destroy): a caller that
+ * returns RunData.electrons = new Electron[final_n] (src/pic.cu:582-584) learns final_n from *out, allocates, and
+ * fetches the records with picb200_download_aos.  Used by the runPIC shim (csrc/runpic_shim.cpp). */
+int picb200_run_keep(const picb200_config* cfg, picb200_summary* out, picb200_sim** sim_out);
 
 /* ---- session API: the phases of runPIC's loop, callable one by one -------------------------- */
 /* allocations + table upload + persistent-grid sizing (src/pic.cu:380-454) */

@@ -85,6 +85,7 @@ SIGNATURES = {
     "picb200_device_count": (C.c_int, []),
     "picb200_config_default": (None, [C.POINTER(Config)]),
     "picb200_run": (C.c_int, [C.POINTER(Config), C.POINTER(Summary), C.c_void_p, C.c_int64]),
+    "picb200_run_keep": (C.c_int, [C.POINTER(Config), C.POINTER(Summary), C.POINTER(_sim)]),
     "picb200_create": (C.c_int, [C.POINTER(Config), C.POINTER(_sim)]),
     "picb200_destroy": (None, [_sim]),
     "picb200_init_uniform": (C.c_int, [_sim, C.c_int32, C.c_uint64]),
@@ -245,6 +246,16 @@ class Sim:
         _check(lib.picb200_download(self._h, C.byref(n), *[_ptr(a, _fp) for a in f], _ptr(ts, _ip), _ptr(id, _up)))
         assert n.value == n_guess
         return State(*f, ts, id)
+
+    def download_aos(self, out=None):
+        """The population as the reference's 64-byte records (src/electron.h:12-18), transposed on the device."""
+        n = C.c_int64(0)
+        if out is None:
+            _check(lib.picb200_download_aos(self._h, None, 0, C.byref(n)))       # cap 0: only the count
+            s = self.summary_raw()
+            out = np.zeros(max(int(s.final_n), 0), dtype=ELECTRON_DTYPE)
+        _check(lib.picb200_download_aos(self._h, out.ctypes.data_as(C.c_void_p), out.shape[0], C.byref(n)))
+        return out[: n.value]
 
     def poisson_step(self):
         _check(lib.picb200_poisson_step(self._h))

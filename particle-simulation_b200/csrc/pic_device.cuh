@@ -464,6 +464,25 @@ __global__ void k_step_end(DevState* st, int capacity, StepLog* log, int log_len
     step_end_body(st, capacity, log, log_len, stop_at_zero);
 }
 
+// The reference's 64-byte AoS record (src/electron.h:12-18: double3 position, double3 velocity, float3 acceleration,
+// int timestamp) built on the device from the SoA store: fp32 state widened to double, four 16-byte stores per electron
+// (replaces a single-threaded transpose on the host; RunData.electrons of src/pic.cu:583 and log() of src/utility.cu:124-137
+// consume this layout).
+struct alignas(16) AosRecord { double px, py, pz, vx, vy, vz; float ax, ay, az; int ts; };
+static_assert(sizeof(AosRecord) == 64, "src/electron.h:12-18");
+__global__ void k_export_aos(Soa s, int first, int count, AosRecord* __restrict__ out) {
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const int i = first + k;
+        double2* o = reinterpret_cast<double2*>(out + k);
+        const float x = __ldcs(s.x + i), y = __ldcs(s.y + i), z = __ldcs(s.z + i);
+        const float vx = __ldcs(s.vx + i), vy = __ldcs(s.vy + i), vz = __ldcs(s.vz + i);
+        __stcs(o + 0, make_double2((double)x, (double)y));
+        __stcs(o + 1, make_double2((double)z, (double)vx));
+        __stcs(o + 2, make_double2((double)vy, (double)vz));
+        __stcs(reinterpret_cast<float4*>(o + 3), make_float4(__ldcs(s.ax + i), __ldcs(s.ay + i), __ldcs(s.az + i), __int_as_float(__ldcs(s.ts + i))));
+    }
+}
+
 #include "pic_mover.cuh"
 
 // device-side known-answer hooks

@@ -820,36 +820,49 @@ int picb200_download(picb200_sim* sim, int32_t* n_out, float* x, float* y, float
     return 0;
 }
 
+// RunData.electrons (src/pic.cu:580-584) / log() (src/utility.cu:124-137): the population as the reference's 64-byte
+// records.  The transpose runs on the device (k_export_aos) in chunks of 4M electrons through two staging buffers, so the
+// copy of one chunk to the host overlaps the transpose of the next; `out` may be pageable or pinned (picb200_alloc_pinned).
 int picb200_download_aos(picb200_sim* sim, picb200_electron* out, int64_t cap, int64_t* n_out) {
     Sim& s = sim->s;
+    CK(cudaSetDevice(s.device), "Set device");
     if (s.sync_state()) return 1;
     const int n_all = std::min(std::max(s.h_st->n, s.h_st->n_alloc), s.cfg.capacity);
-    const int n = (int)std::min<int64_t>(n_all, cap);
-    std::vector<float> f((size_t)n * 9);
-    std::vector<int32_t> ts((size_t)n);
-    int got = 0;
-    float* b = f.data();
-    const size_t N = (size_t)n;
-    // download() copies min(n, capacity) entries; restrict by temporarily using sized buffers
-    if (n_all > n) {
-        std::vector<float> g((size_t)n_all * 9);
-        std::vector<int32_t> t2((size_t)n_all);
-        float* q = g.data();
-        const size_t M = (size_t)n_all;
-        if (picb200_download(sim, &got, q, q + M, q + 2 * M, q + 3 * M, q + 4 * M, q + 5 * M, q + 6 * M, q + 7 * M, q + 8 * M, t2.data(), nullptr)) return 1;
-        for (int k = 0; k < 9; ++k) memcpy(b + (size_t)k * N, q + (size_t)k * M, N * 4);
-        memcpy(ts.data(), t2.data(), N * 4);
-    } else if (n > 0) {
-        if (picb200_download(sim, &got, b, b + N, b + 2 * N, b + 3 * N, b + 4 * N, b + 5 * N, b + 6 * N, b + 7 * N, b + 8 * N, ts.data(), nullptr)) return 1;
-    }
-    for (size_t i = 0; i < N; ++i) {
-        picb200_electron& e = out[i];
-        e.position[0] = b[i]; e.position[1] = b[N + i]; e.position[2] = b[2 * N + i];
-        e.velocity[0] = b[3 * N + i]; e.velocity[1] = b[4 * N + i]; e.velocity[2] = b[5 * N + i];
-        e.acceleration[0] = b[6 * N + i]; e.acceleration[1] = b[7 * N + i]; e.acceleration[2] = b[8 * N + i];
-        e.timestamp = ts[i];
-    }
+    const int n = (int)std::min<int64_t>(n_all, std::max<int64_t>(cap, 0));
     if (n_out) *n_out = n;
+    if (n == 0) return 0;
+    if (!out) return fail("null output buffer", "Download");
+    static_assert(sizeof(AosRecord) == sizeof(picb200_electron), "one record layout");
+    const int chunk = std::min(n, 1 << 22);
+    AosRecord* stage[2] = {nullptr, nullptr};
+    cudaEvent_t done[2] = {nullptr, nullptr};
+    cudaStream_t copy = nullptr;
+    cudaError_t e = cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking);
+    for (int k = 0; k < 2 && e == cudaSuccess; ++k) {
+        if (k == 0 || n > chunk) e = cudaMalloc(&stage[k], (size_t)chunk * sizeof(AosRecord));
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming);
+    }
+    cudaEvent_t filled = nullptr;
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&filled, cudaEventDisableTiming);
+    int b = 0;
+    for (int first = 0; first < n && e == cudaSuccess; first += chunk, b ^= (n > chunk ? 1 : 0)) {
+        const int cnt = std::min(chunk, n - first);
+        e = cudaStreamWaitEvent(s.stream, done[b], 0);                 // the copy that last read this buffer (no-op the first time)
+        if (e != cudaSuccess) break;
+        k_export_aos<<<std::max(1, std::min(s.aux_blocks, (cnt + 255) / 256)), 256, 0, s.stream>>>(s.soa, first, cnt, stage[b]);
+        ++s.launches;
+        e = cudaEventRecord(filled, s.stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(copy, filled, 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(out + first, stage[b], (size_t)cnt * sizeof(AosRecord), cudaMemcpyDeviceToHost, copy);
+        if (e == cudaSuccess) e = cudaEventRecord(done[b], copy);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(copy);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    for (int k = 0; k < 2; ++k) { cudaFree(stage[k]); if (done[k]) cudaEventDestroy(done[k]); }
+    if (filled) cudaEventDestroy(filled);
+    if (copy) cudaStreamDestroy(copy);
+    CK(e, "Download");
     return 0;
 }
 

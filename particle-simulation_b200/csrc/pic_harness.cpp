@@ -115,107 +115,145 @@ int picb200_harness_run(const picb200_config* cfg_in, int gpus) {
     return 0;
 }
 
-// Sort key and comparison of src/electron.h:28-41.
-static std::tuple<int, double, double, double, double, double, double> key_of(const picb200_electron& e) {
-    return std::make_tuple(e.timestamp, e.position[1], e.position[0], e.position[2], e.velocity[1], e.velocity[0], e.velocity[2]);
+// ---------------------------------------------------------------------------------------------
+// `run test ...` and `run bench`: the two harness modes of src/test.cu, as clients of the C ABI.
+// What is shared with the reference is its CONTRACT -- the printf strings a user (or a script) sees, the order of
+// the comparison key (src/electron.h:28-41), the sweep grid and the CSV columns that analyse/plot_pic_*.py read
+// (src/utility.cu:87-93) -- and those must match character for character; the code around them is this
+// repository's own (the reference's own harness, unchanged, runs on this engine too: oracle/_ref_shim/main,
+// csrc/runpic_shim.cpp).
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+// src/electron.h:28-30: (timestamp, y, x, z, vy, vx, vz)
+using SortKey = std::tuple<int, double, double, double, double, double, double>;
+SortKey sort_key(const picb200_electron& e) {
+    return SortKey(e.timestamp, e.position[1], e.position[0], e.position[2], e.velocity[1], e.velocity[0], e.velocity[2]);
 }
-static void print_electron(int i, const picb200_electron& e) {
+bool key_less(const picb200_electron& a, const picb200_electron& b) { return sort_key(a) < sort_key(b); }
+
+void print_electron(int i, const picb200_electron& e) {       // src/electron.h:19-26
     printf("%d: (%.15f, %.15f, %.15f) (%.15f, %.15f, %.15f) ((%.7f, %.7f, %.7f)) [%d]\n", i, e.position[0], e.position[1],
            e.position[2], e.velocity[0], e.velocity[1], e.velocity[2], e.acceleration[0], e.acceleration[1], e.acceleration[2], e.timestamp);
 }
 
+// One scheduler's run with its final population as 64-byte records (src/electron.h:12-18).
+struct SortedRun {
+    int final_n = 0;
+    std::vector<picb200_electron> electrons;
+};
+int run_one(picb200_config cfg, int scheduler, SortedRun& out) {
+    cfg.mode = scheduler;
+    picb200_summary sum;
+    picb200_sim* sim = nullptr;
+    if (picb200_run_keep(&cfg, &sum, &sim)) return 1;
+    out.final_n = (int)sum.final_n;
+    out.electrons.resize((size_t)std::max(out.final_n, 1));
+    int64_t got = 0;
+    const int rc = picb200_download_aos(sim, out.electrons.data(), out.final_n, &got);
+    picb200_destroy(sim);
+    if (rc) return 1;
+    out.electrons.resize((size_t)out.final_n);
+    return 0;
+}
+
+}  // namespace
+
 int picb200_harness_unit_test(const picb200_config* cfg_in) {
-    // src/test.cu:43-100: base scheduler 1 (CPU Sync), then every scheduler against it.  The
-    // reference leaves Naive out because its per-slot RNG makes Naive diverge; with the RNG
-    // keyed on the particle id all four schedulers must agree, so Naive (2) is tested as well.
-    const int base_function = 1;
-    const int test_functions[] = {0, 1, 3, 2};
-    const int amnt = (int)(sizeof(test_functions) / sizeof(int));
-    std::vector<bool> broken((size_t)amnt, false);
-    std::vector<int> final_ns((size_t)amnt, 0);
+    // src/test.cu:43-100 compares schedulers 0, 1, 3 with scheduler 1 (CPU Sync) and leaves Naive out, because the
+    // reference's per-slot RNG makes Naive diverge.  Here the RNG is keyed on the particle id, all four schedulers
+    // must agree, and Naive (2) is compared as well (reported last, so the first three lines read as the reference's).
+    constexpr int kBaseline = 1;
+    const int candidates[] = {0, 1, 3, 2};
+    struct Verdict { int scheduler; bool ok; int final_n; };
+    std::vector<Verdict> verdicts;
 
     picb200_config cfg = *cfg_in;
     cfg.print_stdout = 1;
-    std::vector<picb200_electron> base((size_t)cfg.capacity), cur((size_t)cfg.capacity);
-    picb200_summary sum;
-    cfg.mode = base_function;
-    if (picb200_run(&cfg, &sum, base.data(), cfg.capacity)) return 1;
-    const int base_final_n = (int)sum.final_n;
-    auto less = [](const picb200_electron& a, const picb200_electron& b) { return key_of(a) < key_of(b); };
+    SortedRun base;
+    if (run_one(cfg, kBaseline, base)) return 1;
     printf("Sorting base...\n");
-    std::sort(base.begin(), base.begin() + base_final_n, less);
+    std::sort(base.electrons.begin(), base.electrons.end(), key_less);
     printf("Done sorting base\n");
 
-    for (int fi = 0; fi < amnt; ++fi) {
-        const int function = test_functions[fi];
-        cfg.mode = function;
-        if (picb200_run(&cfg, &sum, cur.data(), cfg.capacity)) return 1;
-        const int final_n = (int)sum.final_n;
-        final_ns[(size_t)fi] = final_n;
-        if (final_n != base_final_n) {
-            printf("\n\nFinal n does not match in %d. Base: %d, test: %d\n\n\n", function, base_final_n, final_n);
-            broken[(size_t)fi] = true;
-            continue;
-        }
-        printf("Sorting %d...\n", function);
-        std::sort(cur.begin(), cur.begin() + final_n, less);
-        printf("Done sorting\n");
-        for (int i = 0; i < final_n; ++i) {
-            if (key_of(base[(size_t)i]) != key_of(cur[(size_t)i])) {
-                printf("Mismatch in %d!\n", function);
-                print_electron(i, base[(size_t)i]);
-                print_electron(i, cur[(size_t)i]);
-                broken[(size_t)fi] = true;
-                break;
-            } else if (cfg.verbose != 0 && i % cfg.verbose == 0) {
-                print_electron(i, base[(size_t)i]);
+    for (int scheduler : candidates) {
+        SortedRun cur;
+        if (run_one(cfg, scheduler, cur)) return 1;
+        Verdict v{scheduler, true, cur.final_n};
+        if (cur.final_n != base.final_n) {
+            printf("\n\nFinal n does not match in %d. Base: %d, test: %d\n\n\n", scheduler, base.final_n, cur.final_n);
+            v.ok = false;
+        } else {
+            printf("Sorting %d...\n", scheduler);
+            std::sort(cur.electrons.begin(), cur.electrons.end(), key_less);
+            printf("Done sorting\n");
+            for (int i = 0; i < cur.final_n; ++i) {
+                if (sort_key(base.electrons[(size_t)i]) != sort_key(cur.electrons[(size_t)i])) {
+                    printf("Mismatch in %d!\n", scheduler);
+                    print_electron(i, base.electrons[(size_t)i]);
+                    print_electron(i, cur.electrons[(size_t)i]);
+                    v.ok = false;
+                    break;
+                }
+                if (cfg.verbose != 0 && i % cfg.verbose == 0) print_electron(i, base.electrons[(size_t)i]);
             }
         }
+        verdicts.push_back(v);
     }
-    printf("\nTests done with following results as compared to %d (%d):\n", base_function, base_final_n);
-    int bad = 0;
-    for (int fi = 0; fi < amnt; ++fi) {
-        printf("%d: %s (%d)\n", test_functions[fi], broken[(size_t)fi] ? "failure" : "success", final_ns[(size_t)fi]);
-        bad += broken[(size_t)fi] ? 1 : 0;
+    printf("\nTests done with following results as compared to %d (%d):\n", kBaseline, base.final_n);
+    int failures = 0;
+    for (const Verdict& v : verdicts) {
+        printf("%d: %s (%d)\n", v.scheduler, v.ok ? "success" : "failure", v.final_n);
+        failures += v.ok ? 0 : 1;
     }
-    return bad ? 3 : 0;
+    return failures ? 3 : 0;
 }
 
 int picb200_harness_bench(const char* csv_path) {
-    // Sweep of src/test.cu:4-41: init n 1e6, max n 5e7, 10 Poisson steps, mobility steps
-    // 10..100 by 10 then 200..1000 by 100, block 128..1024, all four schedulers (Naive only
-    // up to block 256).  CSV columns of src/utility.cu:87-93, read by analyse/plot_pic_*.py.
-    struct Row { std::string func; int init_n, iterations, mobility_steps, block_size, sleep_time, final_n; double time; };
-    std::vector<Row> rows;
-    const int block_sizes[] = {128, 256, 512, 1024};
-    int incr = 10;
-    for (int mobility_steps = incr; mobility_steps <= 1000; mobility_steps += incr) {
-        if (mobility_steps == incr * 10) incr *= 10;
-        for (int block_size : block_sizes) {
-            for (int function = 0; function < 4; ++function) {
-                if (function == 2 && block_size > 256) continue;
+    // The sweep of src/test.cu:4-41: init n 1e6, max n 5e7, 10 Poisson steps, sleep 100 ns; mobility steps 10..100 by
+    // 10 then 200..1000 by 100; block sizes 128..1024; all four schedulers, Naive only up to block 256.
+    // PICB200_BENCH_QUICK=1 (tests): mobility steps {10, 100} x block sizes {256, 1024} -- the cells
+    // analyse/plot_pic_mobility.py:8-12 selects.  PICB200_BENCH_INIT_N overrides the population.
+    const bool quick = getenv("PICB200_BENCH_QUICK") && atoi(getenv("PICB200_BENCH_QUICK")) != 0;
+    const int init_n = getenv("PICB200_BENCH_INIT_N") ? atoi(getenv("PICB200_BENCH_INIT_N")) : 1000000;
+    std::vector<int> mobility_grid, block_grid;
+    if (quick) {
+        mobility_grid = {10, 100};
+        block_grid = {256, 1024};
+    } else {
+        for (int m = 10; m <= 100; m += 10) mobility_grid.push_back(m);
+        for (int m = 200; m <= 1000; m += 100) mobility_grid.push_back(m);
+        block_grid = {128, 256, 512, 1024};
+    }
+    struct CsvRow { const char* func; int init_n, iterations, mobility_steps, block_size, sleep_time, final_n; double time_ms; };
+    std::vector<CsvRow> table;
+    for (int mobility_steps : mobility_grid)
+        for (int block_size : block_grid)
+            for (int scheduler = 0; scheduler < 4; ++scheduler) {
+                if (scheduler == PICB200_MODE_NAIVE && block_size > 256) continue;      // src/test.cu:22
                 picb200_config cfg;
                 picb200_config_default(&cfg);
-                cfg.mode = function;
-                cfg.init_n = 1000000;
+                cfg.mode = scheduler;
+                cfg.init_n = init_n;
                 cfg.capacity = 50000000;
                 cfg.poisson_steps = 10;
                 cfg.poisson_timestep = mobility_steps;
                 cfg.block_size = block_size;
                 cfg.sleep_time_ns = 100;
                 cfg.print_stdout = 1;
+                cfg.table_path = getenv("PICB200_TABLE");
                 picb200_summary sum;
                 if (picb200_run(&cfg, &sum, nullptr, 0)) { printf("%s", picb200_last_error()); return 1; }
-                if (sum.final_n >= cfg.capacity) { printf("\n\n\nIllegal!!!\n\n\n"); continue; }
-                rows.push_back(Row{kSchedulerName[function], cfg.init_n, cfg.poisson_steps, mobility_steps, block_size, 100, (int)sum.final_n, sum.gpu_ms});
+                if (sum.final_n >= cfg.capacity) { printf("\n\n\nIllegal!!!\n\n\n"); continue; }      // src/test.cu:25-29
+                table.push_back(CsvRow{kSchedulerName[scheduler], cfg.init_n, cfg.poisson_steps, mobility_steps, block_size, cfg.sleep_time_ns, (int)sum.final_n, sum.gpu_ms});
             }
-        }
-    }
     FILE* os = fopen(csv_path, "w");
     if (!os) { fprintf(stderr, "cannot write %s\n", csv_path); return 2; }
+    // header and row format of src/utility.cu:87-93; `split chance` is never assigned by the reference
+    // (src/utility.h:23: uninitialised) -- 0 here
     fprintf(os, "func,init n,iterations,mobility steps,block size,sleep time,split chance,final n,time\n");
-    for (const Row& d : rows)
-        fprintf(os, "%s,%d,%d,%d,%d,%d,%f,%d,%f\n", d.func.c_str(), d.init_n, d.iterations, d.mobility_steps, d.block_size, d.sleep_time, 0.0, d.final_n, d.time);
+    for (const CsvRow& r : table)
+        fprintf(os, "%s,%d,%d,%d,%d,%d,%f,%d,%f\n", r.func, r.init_n, r.iterations, r.mobility_steps, r.block_size, r.sleep_time, 0.0, r.final_n, r.time_ms);
     fclose(os);
     return 0;
 }

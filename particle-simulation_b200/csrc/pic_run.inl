@@ -49,8 +49,11 @@ static void naive_step_logger(Sim* s, void* user) {
 
 }  // namespace picb200
 
-extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, picb200_electron* electrons_out,
-                           int64_t electrons_cap) {
+// The whole of runPIC; on success *keep (if given) receives the still-live simulation, so that a caller that does not
+// know final_n in advance can size its buffer first and fetch the population with picb200_download_aos afterwards.
+static int run_impl(const picb200_config* cfg_in, picb200_summary* out, picb200_electron* electrons_out, int64_t electrons_cap,
+                    picb200_sim** keep) {
+    if (keep) *keep = nullptr;
     if (!cfg_in) return fail("null argument", "picb200_run");
     picb200_config cfg = *cfg_in;
     const bool say = cfg.print_stdout != 0;
@@ -130,6 +133,15 @@ extern "C" int picb200_run(const picb200_config* cfg_in, picb200_summary* out, p
         if (out) *out = sum;
         rc = 0;
     } while (0);
-    picb200_destroy(sim);
+    if (rc == 0 && keep) *keep = sim;
+    else picb200_destroy(sim);
     return rc;
+}
+
+extern "C" int picb200_run(const picb200_config* cfg, picb200_summary* out, picb200_electron* electrons_out, int64_t electrons_cap) {
+    return run_impl(cfg, out, electrons_out, electrons_cap, nullptr);
+}
+extern "C" int picb200_run_keep(const picb200_config* cfg, picb200_summary* out, picb200_sim** sim_out) {
+    if (!sim_out) return fail("null argument", "picb200_run_keep");
+    return run_impl(cfg, out, nullptr, 0, sim_out);
 }

@@ -186,10 +186,13 @@ def test_cfg1_reference_smallest_run(engine, oracle, mode):
     assert (summ["final_n"], summ["total_added"], summ["total_removed"], summ["pushes"]) == (10000, 0, 0, 1000000)
     assert (c["n"], c["added"], c["removed"], c["pushes"]) == (10000, 0, 0, 1000000)
     s = o.download()          # no spawns, no deaths -> slot order is the id order on both sides
-    assert np.array_equal(el["position"][:, 0].astype(np.float32), s["x"].astype(np.float32))
-    assert np.array_equal(el["velocity"][:, 1].astype(np.float32), s["vy"].astype(np.float32))
-    assert np.array_equal(el["acceleration"][:, 2], s["az"])
+    assert el.shape[0] == 10000
+    for k, name in enumerate("xyz"):        # all nine columns of the 64-byte record (src/electron.h:12-18), bit for bit
+        assert np.array_equal(el["position"][:, k], s[name].astype(np.float32).astype(np.float64)), f"position.{name}"
+        assert np.array_equal(el["velocity"][:, k], s["v" + name].astype(np.float32).astype(np.float64)), f"velocity.{name}"
+        assert np.array_equal(el["acceleration"][:, k], s["a" + name].astype(np.float32)), f"acceleration.{name}"
     assert np.all(el["timestamp"] == -1)
+    assert np.abs(el["velocity"]).max() > 0 and np.abs(el["acceleration"]).max() > 0
 
 
 def test_run_with_collisions_all_modes_agree(engine, oracle):
