@@ -4,8 +4,11 @@
 Workload (N=1): BASELINE cfg2 = `run 30 0 1000000 100 256 100000000 100 10`: the persistent
 scheduler (mode 30), 1e6 initial electrons, 100 Poisson steps x 10 mobility steps, capacity 1e8,
 shipped cross-section table.  One bench "step" = one complete run of that configuration (~1e9
-pushes).  N>1: every rank runs the same slab size (weak scaling, global init n = N x 1e6) and
-the charge box is all-reduced over NCCL once per Poisson step.
+pushes).  N>1: every rank runs the same slab size (weak scaling, global init n = N x 1e6); the charge box is
+summed across the GPUs INSIDE the persistent kernel by bulk reduce-adds into the peers' memory over NVLink
+(csrc/pic_peer.cuh) -- no NCCL call on the data path (PICB200_NCCL=1 selects the one-all-reduce-per-Poisson-step
+fallback).  Before anything is timed, a run with N > 1 checks itself: a short colliding workload on the N slabs
+must equal the same population on ONE GPU (counts and an order-independent digest of every electron) -> `parity_check`.
 
   value     pushes / device time of the Poisson loop (cudaEvent span, as src/pic.cu:476..:563),
             electrons initialised on the device, L2 flushed between runs.
@@ -16,7 +19,11 @@ the charge box is all-reduced over NCCL once per Poisson step.
             steps): algorithmic bytes = 68 B per push x pushes of the launch, divided by
             its device time (CUDA events on the launching stream) vs measured HBM copy bandwidth.  The
             kernel keeps an electron in registers for all 10 mobility steps, so the 68-B-accounted
-            figure may exceed the HBM peak; `traffic` is the DRAM traffic ncu measured for it.
+            figure may exceed the HBM peak; `traffic` is the DRAM traffic ncu measured for it (a committed capture,
+            labelled with its commit -- not measured in this run).  `issue_frac` is the honest ceiling: pushes/s
+            against 4 warp-instructions per SM and cycle / (warp-instructions per push, same capture).
+  cfg4      BASELINE configs[3]: 1e9 electrons in total sharded over the N GPUs, 10 x 10 steps, device-timed
+            (strong scaling: the per-N values of this sub-record divide the same work).
   --impl reference   times the reference itself: its own CUDA program (oracle/_ref/main, built from
             the upstream sources where they lie) when it and a GPU are available, else the CPU port.
 """
@@ -94,7 +101,8 @@ class ClockSampler:
 
 
 def dist_setup(n_gpus):
-    """Control plane for N>1 (torchrun): gloo for the rendezvous; the data path uses NCCL inside the engine."""
+    """Control plane for N>1 (torchrun): gloo for the rendezvous, the barriers, the max over ranks and the all-gather of
+    the 256-byte peer handles; the data path is the engine's own NVLink peer exchange (no collective library)."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
@@ -156,6 +164,105 @@ def issue_note():
             "registers_per_thread": t.get("registers_per_thread"), "source": f"profiles ncu capture, commit {t['commit']}"}
 
 
+def state_digest(d):
+    """Order-independent digest of a population: per-electron 64-bit mix of the id and the raw fp32 bits of position and
+    velocity; (sum mod 2^64, xor) -- both combine across ranks."""
+    import numpy as np
+    h = d.id.astype(np.uint64).copy()
+    for k in ("x", "y", "z", "vx", "vy", "vz"):
+        h = (h * np.uint64(0x9E3779B97F4A7C15)) ^ getattr(d, k).view(np.uint32).astype(np.uint64)
+    return int(h.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(h)) if h.size else 0
+
+
+def connect_peers(dist, sim, world):
+    handles = [None] * world
+    dist.all_gather_object(handles, sim.peer_export())
+    sim.peer_connect(handles)
+    dist.barrier()
+
+
+def parity_check(eng, dist, rank, world, local, uid):
+    """N slabs == one GPU (the reference has no multi-GPU path, src/pic.cu:394, so this is the only oracle there is for
+    N > 1; tests/test_multi_gpu.py compares the same thing with the CPU oracle).  A hot, dense population (collisions from
+    the first push, several electrons per cell) runs 5 + 7 Poisson steps in two launches on the N slabs; counts and the
+    digest are combined over the ranks and compared with the same population on rank 0's GPU alone.  Untimed."""
+    import numpy as np
+    n, pt, steps = 64000 * world, 10, (5, 7)
+    cap = 16 * n
+    rng = np.random.default_rng(3)
+    pos = rng.uniform(2.45, 2.65, size=(3, n)).astype(np.float32)
+    vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)
+    lo, hi = n * rank // world, n * (rank + 1) // world
+    sim = eng.Sim(mode=0, capacity=cap // world, poisson_timestep=pt, poisson_steps=sum(steps), device=local, rank=rank, nranks=world, nccl_unique_id=uid)
+    if uid is None:
+        connect_peers(dist, sim, world)
+    sim.upload(*[a[lo:hi] for a in pos], *[a[lo:hi] for a in vel], id=np.arange(lo, hi, dtype=np.uint64))
+    dist.barrier()
+    for k in steps:
+        sim.run_steps(k)
+    m = sim.summary()
+    mine = (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) + state_digest(sim.download())
+    dist.barrier()                       # no rank frees a grid a peer may still map
+    sim.close()
+    parts = [None] * world
+    dist.all_gather_object(parts, mine)
+    got = [sum(p[k] for p in parts) for k in range(4)] + [sum(p[4] for p in parts) % (1 << 64)]
+    x = 0
+    for p in parts:
+        x ^= p[5]
+    got.append(x)
+    res = [None]
+    if rank == 0:
+        with eng.Sim(mode=0, capacity=cap, poisson_timestep=pt, poisson_steps=sum(steps), device=local) as one:
+            one.upload(*pos, *vel, id=np.arange(n, dtype=np.uint64))
+            for k in steps:
+                one.run_steps(k)
+            m1 = one.summary()
+            exp = [m1["final_n"], m1["total_added"], m1["total_removed"], m1["pushes"]] + list(state_digest(one.download()))
+        res[0] = {"ok": got == exp, "n_initial": n, "final_n": got[0], "added": got[1], "removed": got[2], "pushes": got[3],
+                  "digest": "%016x:%016x" % (got[4], got[5]), "transport": "nccl" if uid is not None else "peer",
+                  "what": f"{world} slabs vs the same population on one GPU: counts and (sum, xor) digest of (id, position, velocity) of every electron"}
+        if not res[0]["ok"]:
+            res[0]["expected"] = exp
+            res[0]["got"] = got
+    dist.broadcast_object_list(res, src=0)
+    return res[0]
+
+
+CFG4 = dict(mode=0, init_n=1000000000, poisson_steps=10, block_size=256, capacity=1600000000, sleep_time_ns=100, poisson_timestep=10)
+
+
+def cfg4_record(eng, dist, rank, world, local, uid, runs=3):
+    """BASELINE configs[3]: 1e9 electrons in total, sharded over the N GPUs (N = 1: 48 GB on one B200), 10 Poisson x 10
+    mobility steps, capacity 1.6e9 in total.  Device-timed, 1 warm-up + `runs` timed runs, max over ranks."""
+    kw = dict(CFG4)
+    kw["capacity"] = CFG4["capacity"] // world
+    sim = eng.Sim(device=local, rank=rank, nranks=world, nccl_unique_id=uid, **kw)
+    if world > 1 and uid is None:
+        connect_peers(dist, sim, world)
+    n = CFG4["init_n"]
+    lo, hi = n * rank // world, n * (rank + 1) // world
+    ms, pushes, final_n = [], 0, 0
+    for it in range(1 + runs):
+        sim.init_uniform(hi - lo, lo)
+        if dist is not None:
+            dist.barrier()
+        sim.run_steps(CFG4["poisson_steps"])
+        m = sim.summary()
+        if it > 0:
+            ms.append(all_max(dist, m["gpu_ms"]))
+            pushes += m["pushes"]
+        final_n = m["final_n"]
+    if dist is not None:
+        dist.barrier()
+    sim.close()
+    pushes_all = all_sum(dist, float(pushes))
+    final_all = all_sum(dist, float(final_n))
+    return {"workload": "cfg4: 1e9 electrons in total sharded over the GPUs, run 30 0 1000000000 10 256 1600000000 100 10", "scaling": "strong",
+            "value": pushes_all / (sum(ms) / 1e3), "unit": UNIT, "ms_per_run": sum(ms) / len(ms), "ms_runs": ms, "runs": runs,
+            "final_n": int(final_all), "pushes_per_run": int(pushes_all) // runs, "timing": "cudaEvent span of the Poisson loop on the engine's stream, max over ranks"}
+
+
 def cpu_baseline(budget_s=12.0):
     """The CPU port (oracle/, OpenMP over all host cores) on a bounded sample of cfg2: its first
     Poisson steps until ~budget_s of wall time is used."""
@@ -188,15 +295,20 @@ def run_ours(args):
         obj = [eng.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(obj, src=0)
         uid = obj[0]
+    # ---- N > 1: the N slabs must equal one GPU before anything is timed (exit code 2 otherwise)
+    parity = None
+    if world > 1 and not os.environ.get("PICB200_BENCH_NO_PARITY"):
+        parity = parity_check(eng, dist, rank, world, local, uid)
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "n_gpus": world, "parity_check": parity, "error": "multi-GPU run differs from the single-GPU run"}), flush=True)
+            raise SystemExit(2)
     n_local = CFG2["init_n"]
     kw = dict(CFG2)
     kw["init_n"] = n_local * world
     sim = eng.Sim(device=local, rank=rank, nranks=world, nccl_unique_id=uid, **kw)
     if world > 1 and not use_nccl:
-        handles = [None] * world
-        dist.all_gather_object(handles, sim.peer_export())
-        sim.peer_connect(handles)
-        dist.barrier()
+        connect_peers(dist, sim, world)
     id_base = rank * n_local
     P = CFG2["poisson_steps"]
 
@@ -229,8 +341,8 @@ def run_ours(args):
     gpu_ms = 0.0
     barrier()
     for _ in range(args.steps):
-        sim.flush_l2()
         sim.init_uniform(n_local, id_base)
+        sim.flush_l2()                     # after the init: the population it wrote is not L2-resident at t0
         barrier()
         sim.run_steps(P)
         s = sim.summary()
@@ -264,7 +376,37 @@ def run_ours(args):
     sim.init_uniform(n_local, id_base)
     sim.run_steps(P)
     phases = sim.profile()
+    barrier()                              # no rank frees a grid a peer may still map
     sim.close()
+
+    # ---- the drop-in call itself (N = 1): picb200_run(cfg, &summary, electrons_out, cap) -- what the runPIC shim
+    # makes (csrc/runpic_shim.cpp) -- allocation, init, the run and the 64-byte AoS population into a pinned host buffer
+    dropin = None
+    if world == 1 and not os.environ.get("PICB200_BENCH_NO_DROPIN"):
+        import ctypes as C
+        buf = eng.pinned_empty(cap_host, eng.ELECTRON_DTYPE)
+        cfg, keep = eng.make_config(**CFG2)
+        walls, dpush, dn = [], 0, 0
+        for it in range(3):
+            sm = eng.Summary()
+            t0 = time.perf_counter()
+            rc = eng.lib.picb200_run(C.byref(cfg), C.byref(sm), buf.ctypes.data_as(C.c_void_p), cap_host)
+            dt = time.perf_counter() - t0
+            if rc != 0:
+                raise SystemExit("bench.py: picb200_run failed: " + eng.lib.picb200_last_error().decode(errors="replace"))
+            if it > 0:
+                walls.append(dt)
+                dpush += sm.pushes
+                dn = int(sm.final_n)
+        dropin = {"value": dpush / sum(walls), "unit": UNIT, "wall_ms_per_run": 1e3 * sum(walls) / len(walls), "gpu_ms_last": sm.gpu_ms, "d2h_bytes_per_run": dn * 64,
+                  "what": "picb200_run(): create (all device allocations) + init on the device + 100 Poisson steps + 64-byte AoS export (device transpose) into a pinned host buffer + destroy, wall clock; the reference's `GPU time of program` excludes its allocations"}
+
+    cfg4 = None
+    if not os.environ.get("PICB200_BENCH_NO_CFG4"):
+        try:
+            cfg4 = cfg4_record(eng, dist, rank, world, local, uid)
+        except eng.EngineError as e:       # e.g. a smaller GPU: the headline line is still printed
+            cfg4 = {"error": str(e)}
 
     t_max = all_max(dist, gpu_ms / 1e3)
     e2e_max = all_max(dist, e2e_s)
@@ -276,21 +418,35 @@ def run_ours(args):
     mover_s = prof["mover_ms"] / 1e3
     achieved = pushes * BYTES_PER_PUSH / mover_s / 1e9 if mover_s > 0 else None
     traffic, traffic_note = ncu_traffic(pushes / max(1, int(prof["mover_launches"])))
+    note = issue_note()
+    rate1 = pushes / mover_s if mover_s > 0 else None       # rank 0's own kernel rate
+    issue = None
+    if note and rate1 and clocks and clocks.get("sm_mhz"):
+        ceiling = 4.0 * final["sm_count"] * clocks["sm_mhz"] * 1e6 / note["warp_instructions_per_push"]
+        issue = {"issue_ceiling_pushes_per_s": ceiling, "issue_frac": rate1 / ceiling,
+                 "how": "4 warp-instructions per SM and cycle x SMs x SM clock sampled in this run / warp-instructions per push of the committed ncu capture", "source": note["source"]}
     line = {
         "metric": METRIC, "value": pushes_all / t_max, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_max * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "per_gpu_init_n": n_local, "global_init_n": n_local * world, "final_n_rank0": final["final_n"],
                    "pushes_per_step_rank0": pushes // max(1, args.steps), "parallelism": (f"particle slabs x{world}, " + ("NCCL all-reduce of the charge box per Poisson step" if use_nccl else "charge box summed inside the persistent kernel over NVLink peer memory")) if world > 1 else "single GPU",
-                   "l2": "flushed between runs (512 MiB memset); the 48 MB working set is L2-resident within a run, as it is for the reference"},
+                   "collective": ("ncclAllReduce(int32, sum) per Poisson step" if use_nccl else "none: in-kernel TMA bulk reduce-adds into the peers' memory over NVLink (no NCCL call on the data path)") if world > 1 else "none",
+                   "l2": "flushed after the population is initialised, before every timed run (512 MiB memset > 126 MB L2); the 48 MB working set then stays L2-resident within a run, as it does for the reference"},
         "e2e": {"value": e2e_pushes_all / e2e_max, "unit": UNIT, "h2d_bytes_per_step": n_local * 48, "d2h_bytes_per_step": d2h_bytes // max(1, args.steps),
                 "what": "picb200_upload (pinned host SoA) + picb200_run_steps + picb200_download (pinned host SoA), wall clock"},
         "gpu_launches": int(prof["launches"]),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_note": traffic_note,
+                     "traffic_source": "static profile (committed ncu capture, not measured in this run)",
+                     "binding_resource": "instruction issue (the kernel moves ~1 B/push through DRAM); `frac` is the 68-B step-synchronous equivalent, see issue_frac",
+                     "issue_frac": issue["issue_frac"] if issue else None, "issue": issue,
                      "kernel": "k_poisson_fused", "launches": int(prof["mover_launches"]), "kernel_ms_total": prof["mover_ms"],
                      "kernel_share_of_step": prof["mover_ms"] / gpu_ms if gpu_ms else None,
                      "accounting": f"{BYTES_PER_PUSH:.0f} B per push x pushes per launch (SURVEY.md 8d); peak = {peak_src}; electrons stay in registers for all 10 mobility steps of a launch, so required HBM traffic is ~7.6 B/push and the 68-B-accounted figure may exceed the peak"},
-        "issue_bound_note": issue_note(),
+        "issue_bound_note": note,
+        "parity_check": parity,
+        "e2e_dropin": dropin,
+        "cfg4": cfg4,
         "phases_ms_per_step": {k: v for k, v in phases.items() if k.endswith("_ms")},
         "clocks": clocks,
     }

@@ -87,6 +87,38 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
 }
 __device__ __forceinline__ int ld_volatile_i32(const int* p) { return *(const volatile int*)p; }
 
+// A grid barrier of a persistent kernel that is never completed (a block left the kernel early, or the launch was
+// not co-resident) must not spin for ever: after g_barrier_timeout_ns the waiting block records {code, block, barrier
+// number} in page-locked HOST memory (readable after the context has failed) and traps; the host call then returns
+// "CUDA error: ...\nAt: Mobility steps" (src/utility.cu:108-115) naming the barrier.  Set per device at picb200_create.
+__device__ int* g_abort_flag = nullptr;
+__device__ unsigned long long g_barrier_timeout_ns = 30ull * 1000ull * 1000ull * 1000ull;
+__device__ __forceinline__ unsigned long long timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __noinline__ void barrier_timeout_abort(int code, unsigned seq) {
+    int* flag = g_abort_flag;
+    if (flag) {
+        flag[1] = (int)blockIdx.x; flag[2] = (int)seq; flag[3] = (int)gridDim.x;
+        __threadfence_system();
+        *(volatile int*)flag = code;
+        __threadfence_system();
+    }
+    __trap();
+}
+// spin until *word >= target (acquire), with the time-out above
+__device__ __forceinline__ void barrier_spin(const unsigned* word, unsigned target, int code, unsigned seq) {
+    if (ld_acquire_u32(word) >= target) return;
+    const unsigned long long t0 = timer_ns(), limit = g_barrier_timeout_ns;
+    unsigned spins = 0;
+    while (ld_acquire_u32(word) < target) {
+        __nanosleep(32);
+        if ((++spins & 255u) == 0u && timer_ns() - t0 > limit) barrier_timeout_abort(code, seq);
+    }
+}
+
 // Philox4x32-10 (Salmon et al. SC'11).  Replaces the per-slot XORWOW state of
 // src/random.cu:3-12: no state array, keyed on (seed, particle id, step block).
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {

@@ -103,6 +103,19 @@ static void build_cell_bounds(float* bnd) {
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// Page-locked words the kernels of a device write when a grid barrier times out (barrier_timeout_abort): one set per
+// device for the life of the process -- they must stay readable after the CUDA context has failed.
+static int* g_host_abort[64] = {nullptr};
+static int* abort_words(int device) { return (device >= 0 && device < 64) ? g_host_abort[device] : nullptr; }
+static std::string abort_message(int device) {
+    const int* w = abort_words(device);
+    if (!w || w[0] == 0) return std::string();
+    char buf[256];
+    snprintf(buf, sizeof buf, "grid barrier %d of the persistent kernel timed out: block %d of %d waited, not every block arrived (%s)",
+             w[2], w[1], w[3], w[0] == 1 ? "k_mover" : w[0] == 2 ? "k_poisson_fused" : "peer exchange");
+    return std::string(buf);
+}
+
 struct Sim {
     picb200_config cfg{};
     int device = 0;
@@ -274,6 +287,14 @@ int Sim::create(const picb200_config* c) {
     aux_blocks = sm_count * 8;
     efc = (-1.602176487e-19 * -1.602176487e-19) / (4 * 3.1415926536 * 8.8541878176E-12 * 1e-2 * 1e-2 * 9.1093837015e-31);  // src/cell.cu:5
 
+    if (device < 64) {
+        if (!g_host_abort[device]) { CK(cudaMallocHost(&g_host_abort[device], 4 * sizeof(int)), "Minor alloc"); memset(g_host_abort[device], 0, 4 * sizeof(int)); }
+        int* dev_view = nullptr;
+        CK(cudaHostGetDevicePointer(&dev_view, g_host_abort[device], 0), "Minor alloc");
+        CK(cudaMemcpyToSymbol(g_abort_flag, &dev_view, sizeof(dev_view)), "Minor alloc");
+        const unsigned long long ns = (unsigned long long)(getenv("PICB200_BARRIER_TIMEOUT_MS") ? std::max(1, atoi(getenv("PICB200_BARRIER_TIMEOUT_MS"))) : 30000) * 1000000ull;
+        CK(cudaMemcpyToSymbol(g_barrier_timeout_ns, &ns, sizeof(ns)), "Minor alloc");
+    }
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "Stream");
     CK(cudaEventCreate(&ev_start), "Event");
     CK(cudaEventCreate(&ev_stop), "Event");
@@ -449,7 +470,13 @@ int Sim::peer_connect(const void* handles) {
 int Sim::sync_state() {
     CK(cudaMemcpyAsync(h_st, st, sizeof(DevState), cudaMemcpyDeviceToHost, stream), "State readback");
     if (pl) CK(cudaMemcpyAsync(h_pl, pl, sizeof(PeerLocal), cudaMemcpyDeviceToHost, stream), "State readback");
-    CK(cudaStreamSynchronize(stream), "State readback");
+    {
+        const cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) {                  // a kernel died: say which barrier gave up, if one did (barrier_timeout_abort)
+            const std::string why = abort_message(device);
+            return fail(why.empty() ? std::string(cudaGetErrorString(e)) : why + " [" + cudaGetErrorString(e) + "]", why.empty() ? "State readback" : "Mobility steps");
+        }
+    }
     cur = h_st->cur;
     if (pl && h_pl->error) return fail("a peer rank did not reach the charge exchange within 20 s", "Charge exchange");
     if (h_st->error == 2) return fail("more children waited for a compaction than the parking area holds", "Mobility phase");
@@ -653,7 +680,7 @@ int Sim::fused_steps(int steps) {
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy,
                     std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt)),
-                    field, field_ratio};
+                    field, field_ratio, getenv("PICB200_TEST_DESERT") ? 1 : 0};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
@@ -932,7 +959,8 @@ int picb200_get_profile(picb200_sim* sim, picb200_profile* out) {
 int picb200_flush_l2(picb200_sim* sim) {
     Sim& s = sim->s;
     CK(cudaSetDevice(s.device), "Set device");
-    CK(cudaMemsetAsync(s.grid[(s.cur + 1) % kRot], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
+    // peer mode: grids 0/1 are the summed grids the PEERS add into (never written from the host); grid 2 is this rank's alone
+    CK(cudaMemsetAsync(s.grid[s.peer_connected ? 2 : (s.cur + 1) % kRot], 0, (size_t)kGrid * kGrid * kGrid * 4, s.stream), "Flush L2");
     CK(cudaStreamSynchronize(s.stream), "Flush L2");
     return 0;
 }

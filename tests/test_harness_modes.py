@@ -119,3 +119,14 @@ def test_reference_harness_runs_on_the_engine(tmp_path):
     assert a.returncode == 0 and b.returncode == 0, a.stdout[-1000:] + a.stderr[-1000:]
     assert _stable(a.stdout) == _stable(b.stdout)
     assert sum(1 for ln in a.stdout.splitlines() if ln.startswith("Time ")) == 4
+
+
+@pytest.mark.gpu
+def test_grid_barrier_times_out_instead_of_spinning_for_ever():
+    """A block that never reaches a grid barrier (PICB200_TEST_DESERT=1: the last block leaves the persistent kernel at
+    once) must surface as the reference's two error lines (src/utility.cu:108-115) and a non-zero exit code, not as a hang."""
+    env = dict(os.environ, PICB200_TEST_DESERT="1", PICB200_BARRIER_TIMEOUT_MS="300")
+    r = subprocess.run([PIC_RUN, "30", "0", "5000", "2", "256", "100000", "100", "5"], capture_output=True, text=True, cwd=ROOT, timeout=120, env=env)
+    assert r.returncode != 0
+    assert "CUDA error: grid barrier" in r.stdout and "timed out" in r.stdout and "\nAt: Mobility steps\n" in r.stdout, r.stdout[-1500:]
+    assert "Final amount of particles" not in r.stdout
