@@ -1,5 +1,8 @@
 #!/usr/bin/env python3
-"""Regenerates src/cross_section.txt, the 10 000-row collision table the engine reads.
+"""Generates collision tables in the format of src/cross_section.txt (10 000 rows) -- used for the synthetic
+supercritical tables of BASELINE cfg3.  src/cross_section.txt itself is the REFERENCE'S FILE, byte for byte, and is not
+produced by this script: regenerating it gives the same fp32 values (pinned by tests/test_table.py) but 16 rows differ in
+the last printed digit with this libm -- only the fp32 equality is guaranteed.
 
 Row i holds `split_chance remove_chance` in percent, both equal to
 (sin(i**2.6 / 5e7) + 1.01) * i**0.1 -- the formula the upstream project documents
