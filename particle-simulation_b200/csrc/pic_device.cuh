@@ -19,6 +19,7 @@ constexpr int kRows = 10000;            // src/cross_section.h:9
 constexpr int kDead = -2;               // src/electron.h:8
 constexpr int kGrids = 3;               // charge grids in rotation (gather / next deposit / being emptied)
 constexpr int kRot = 3;
+constexpr int kBoxes = kGrids + 1;      // bounding-box slots in DevState
 constexpr unsigned kFull = 0xffffffffu;
 constexpr uint32_t kTagCollide = 0u, kTagInit = 1u;
 
@@ -43,7 +44,8 @@ struct DevState {
     int n_holes, n_movers;  // compaction work lists
     int gen_hi;             // end of the fall-back window agreed at the barrier (-1: none)
     int n_unfinished;       // children spilled to the global store before they were pushed to the end
-    int bbox_lo[kGrids][3], bbox_hi[kGrids][3];  // cell bounding box of the counts deposited in each charge grid
+    int bbox_lo[kBoxes][3], bbox_hi[kBoxes][3];  // cell bounding box of the counts deposited in each charge grid (peer mode: slots 2 and 3
+                                                 // alternate as the box of the local deposit, slots 0/1 mirror the union boxes of S[0]/S[1])
     int cur;                // which of the charge grids holds the current deposit
     int poisson_index;      // Poisson steps completed
     int hit_zero;           // population reached 0 (src/pic.cu:556-559)
@@ -289,10 +291,10 @@ __device__ __forceinline__ void clear_box_body(const DevState* st, int* __restri
 }
 __global__ void k_clear_box(const DevState* st, int* __restrict__ charge, int which) { clear_box_body(st, charge, which); }
 __global__ void k_set_n(DevState* st, int n) { st->n = n; st->n_alloc = n; st->top_alloc = n; }
-// which: 0 .. kGrids-1 = that grid's box, kGrids = all
+// which: 0 .. kGrids-1 = that grid's box, kGrids = all slots
 __global__ void k_reset_bbox(DevState* st, int which) {
     if (threadIdx.x < 3)
-        for (int g = 0; g < kGrids; ++g)
+        for (int g = 0; g < kBoxes; ++g)
             if (which == g || which == kGrids) { st->bbox_lo[g][threadIdx.x] = kGrid; st->bbox_hi[g][threadIdx.x] = -1; }
 }
 

@@ -135,6 +135,7 @@ struct Sim {
     void* soa_base = nullptr;
     float4* field = nullptr;             // fused kernel, one rank: dense per-cell field for dense plasmas (field_rows), 2 GiB
     int field_ratio = 2;                 // electrons per cell of the occupied box from which it is used (PICB200_FIELD_RATIO; < 0: never)
+    int field_min_n = 0;                 // ... and electrons on this rank (PICB200_FIELD_MIN_N)
     int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
@@ -156,7 +157,7 @@ struct Sim {
     int* d_bbox_red = nullptr;
     int* h_bbox_red = nullptr;
     // multi-GPU, peer mode: the exchange runs inside the fused kernel over NVLink peer mappings
-    PeerMailbox* mail = nullptr;         // written by the peers
+    PeerSync* psync = nullptr;           // arrival counters and union-box words, written by the peers' remote atomics
     PeerLocal* pl = nullptr;
     PeerLocal* h_pl = nullptr;           // pinned mirror
     PeerArgs pa{};
@@ -244,7 +245,7 @@ void Sim::release() {
     if (stream) { cudaStreamSynchronize(stream); }
     for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
     ipc_opened.clear();
-    cudaFree(mail); mail = nullptr;
+    cudaFree(psync); psync = nullptr;
     cudaFree(pl); pl = nullptr;
     if (h_pl) { cudaFreeHost(h_pl); h_pl = nullptr; }
     cudaFree(soa_base); soa_base = nullptr;
@@ -374,16 +375,26 @@ int Sim::create(const picb200_config* c) {
     CK(cudaFuncSetAttribute(k_poisson_fused<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
     fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
     if (const char* fr = getenv("PICB200_FIELD_RATIO")) field_ratio = atoi(fr);
-    if (fused && cfg.nranks == 1 && field_ratio >= 0)        // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
+    // several ranks: the pass over the union box and its grid barrier are paid per rank whatever the slab holds: large slabs only
+    field_min_n = getenv("PICB200_FIELD_MIN_N") ? atoi(getenv("PICB200_FIELD_MIN_N")) : (cfg.nranks > 1 ? 3000000 : 0);
+    if (fused && field_ratio >= 0 && (cfg.nranks == 1 || !cfg.nccl_unique_id))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
         CK(cudaMalloc(&field, (size_t)kGrid * kGrid * kGrid * sizeof(float4)), "Grid alloc");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
     if (cfg.nranks > 1) {
         if (cfg.nranks > kMaxRanks) return fail("at most 8 ranks", "picb200_create");
-        CK(cudaMalloc(&mail, sizeof(PeerMailbox)), "Minor alloc");
-        CK(cudaMemsetAsync(mail, 0, sizeof(PeerMailbox), stream), "Minor alloc");
-        CK(cudaMalloc(&pl, sizeof(PeerLocal)), "Minor alloc");
-        CK(cudaMemsetAsync(pl, 0, sizeof(PeerLocal), stream), "Minor alloc");
+        {
+            PeerSync init;
+            memset(&init, 0, sizeof(init));
+            PeerLocal pl0;
+            memset(&pl0, 0, sizeof(pl0));
+            for (int p = 0; p < 2; ++p)
+                for (int k = 0; k < 3; ++k) { init.box_lo[p][k] = kGrid; init.box_hi[p][k] = -1; pl0.sbox_lo[p][k] = kGrid; pl0.sbox_hi[p][k] = -1; }
+            CK(cudaMalloc(&psync, sizeof(PeerSync)), "Minor alloc");
+            CK(cudaMemcpy(psync, &init, sizeof(init), cudaMemcpyHostToDevice), "Minor alloc");
+            CK(cudaMalloc(&pl, sizeof(PeerLocal)), "Minor alloc");
+            CK(cudaMemcpy(pl, &pl0, sizeof(pl0), cudaMemcpyHostToDevice), "Minor alloc");
+        }
         CK(cudaMallocHost(&h_pl, sizeof(PeerLocal)), "Minor alloc");
         memset(h_pl, 0, sizeof(PeerLocal));
         if (cfg.nccl_unique_id) {            // NCCL path (baseline / no peer access): one communicator per rank
@@ -403,26 +414,28 @@ int Sim::create(const picb200_config* c) {
 }
 
 // What one rank tells the others (picb200_peer_export -> picb200_peer_connect): where its two local
-// deposit grids and its mailbox live.  Same process (one host thread per GPU): raw pointers + peer access.
+// summed grids and its sync block (arrival counters, union-box words) live.  Same process (one host thread per GPU): raw pointers + peer access.
 // Other process (one process per GPU, e.g. torchrun): CUDA IPC handles.
 struct PeerHandle {
     unsigned magic;
     int device;
     long long pid;
-    void* raw[3];                    // summed grid 0, summed grid 1, mailbox
+    void* raw[3];                    // summed grid 0, summed grid 1, sync block
+    int sm_count;                    // blocks of the persistent kernel: every rank counts nranks x blocks arrivals per exchange
     cudaIpcMemHandle_t ipc[3];
 };
 static_assert(sizeof(PeerHandle) <= PICB200_PEER_HANDLE_BYTES, "handle fits the ABI blob");
 
 int Sim::peer_export(void* out) {
-    if (cfg.nranks < 2 || !mail) return fail("peer export needs nranks > 1", "Peer setup");
+    if (cfg.nranks < 2 || !psync) return fail("peer export needs nranks > 1", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
     PeerHandle h;
     memset(&h, 0, sizeof(h));
     h.magic = 0x50494342u;
     h.device = device;
     h.pid = (long long)getpid();
-    h.raw[0] = grid[0]; h.raw[1] = grid[1]; h.raw[2] = mail;
+    h.raw[0] = grid[0]; h.raw[1] = grid[1]; h.raw[2] = psync;
+    h.sm_count = sm_count;
     for (int k = 0; k < 3; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
     memset(out, 0, PICB200_PEER_HANDLE_BYTES);
     memcpy(out, &h, sizeof(h));
@@ -430,7 +443,7 @@ int Sim::peer_export(void* out) {
 }
 
 int Sim::peer_connect(const void* handles) {
-    if (cfg.nranks < 2 || !mail) return fail("peer connect needs nranks > 1", "Peer setup");
+    if (cfg.nranks < 2 || !psync) return fail("peer connect needs nranks > 1", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
     memset(&pa, 0, sizeof(pa));
     pa.rank = cfg.rank;
@@ -440,9 +453,10 @@ int Sim::peer_connect(const void* handles) {
         PeerHandle h;
         memcpy(&h, static_cast<const unsigned char*>(handles) + (size_t)r * PICB200_PEER_HANDLE_BYTES, sizeof(h));
         if (h.magic != 0x50494342u) return fail("bad peer handle", "Peer setup");
+        if (h.sm_count != sm_count) return fail("the ranks' GPUs have different SM counts (the exchange counts one arrival per block of every rank)", "Peer setup");
         void* p[3] = {nullptr, nullptr, nullptr};
         if (r == cfg.rank) {
-            p[0] = grid[0]; p[1] = grid[1]; p[2] = mail;
+            p[0] = grid[0]; p[1] = grid[1]; p[2] = psync;
         } else if (h.pid == (long long)getpid()) {
             int can = 0;
             CK(cudaDeviceCanAccessPeer(&can, device, h.device), "Peer setup");
@@ -459,7 +473,7 @@ int Sim::peer_connect(const void* handles) {
         }
         pa.sum[r][0] = static_cast<int*>(p[0]);
         pa.sum[r][1] = static_cast<int*>(p[1]);
-        pa.mail[r] = static_cast<PeerMailbox*>(p[2]);
+        pa.sync[r] = static_cast<PeerSync*>(p[2]);
     }
     // connect before the first population is created (the grids are still all-zero then)
     if (charge_valid) return fail("picb200_peer_connect must precede the first Poisson step", "Peer setup");
@@ -478,7 +492,6 @@ int Sim::sync_state() {
         }
     }
     cur = h_st->cur;
-    if (pl && h_pl->error) return fail("a peer rank did not reach the charge exchange within 20 s", "Charge exchange");
     if (h_st->error == 2) return fail("more children waited for a compaction than the parking area holds", "Mobility phase");
     if (h_st->error == 3) return fail("a spilled child found no slot below the capacity", "Mobility phase");
     return collect_spans();
@@ -680,7 +693,7 @@ int Sim::fused_steps(int steps) {
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy,
                     std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt)),
-                    field, field_ratio, getenv("PICB200_TEST_DESERT") ? 1 : 0};
+                    (peer || cfg.nranks == 1) ? field : nullptr, field_ratio, field_min_n, getenv("PICB200_TEST_DESERT") ? 1 : 0};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");

@@ -403,6 +403,7 @@ struct FusedArgs {
     int drain_at;                // staged children from which a warp pushes a batch between two chunks (kFusedDrainAt, PICB200_DRAIN_AT)
     float4* field;               // dense 512^3 per-cell field (field_rows), or nullptr
     int field_ratio;             // a Poisson step computes the field per cell when n >= field_ratio * cells of the occupied box (< 0: never)
+    int field_min_n;             // ... and the rank holds at least this many electrons (peer mode: the pass costs a barrier per rank)
     int test_desert;             // PICB200_TEST_DESERT=1 (tests): the last block leaves the kernel at once -> the grid barrier must time out
 };
 
@@ -501,6 +502,7 @@ struct BlockBc {
     int box_new[6];                 // peer mode: box of this step's own (local) deposit
     int box_cur[6];                 // box of the grid this step gathers from
     int use_field;                  // this step gathers from the per-cell field (field_rows)
+    int peer_box[6], peer_box_valid; // peer mode: union box of the exchange just completed (peer_finish -> fetch_step_start)
 };
 
 struct FusedCtx {
@@ -961,13 +963,27 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         bc.hw = launch_start ? bc.n : v->hw;
         s_ticket = 0;
         for (int k = 0; k < 6; ++k) s_box[k] = k < 3 ? kGrid : -1;
-        const int old = kPeer ? (int)(e_done & 1u) : (bc.cur + 2) % kRot;
-        load_box(bc.box_old, v->bbox_lo[old], v->bbox_hi[old]);
+        if (kPeer) {                                         // the box of S[e_done&1]: just received, or (start of a launch) kept
+            const int p = (int)(e_done & 1u);                //  in PeerLocal, which upload / init do not reset
+            const volatile PeerLocal* pl = a.peer.pl;
+            for (int k = 0; k < 3; ++k) {
+                bc.box_old[k] = bc.peer_box_valid ? bc.peer_box[k] : pl->sbox_lo[p][k];
+                bc.box_old[3 + k] = bc.peer_box_valid ? bc.peer_box[3 + k] : pl->sbox_hi[p][k];
+            }
+            bc.peer_box_valid = 0;
+        } else {
+            const int old = (bc.cur + 2) % kRot;
+            load_box(bc.box_old, v->bbox_lo[old], v->bbox_hi[old]);
+        }
+        // dense plasma: this step gathers from the per-cell field (field_rows).  The same words in every block: the same
+        // decision.  Peer mode: the grid gathered from is S[e_done&1], its box the union box (bc.box_old); the pass and its
+        // barrier are paid per rank whatever the slab holds, so the slab must also be large (field_min_n)
+        if (!kPeer) load_box(bc.box_cur, v->bbox_lo[bc.cur], v->bbox_hi[bc.cur]);
+        else for (int k = 0; k < 6; ++k) bc.box_cur[k] = bc.box_old[k];
         bc.use_field = 0;
-        if (!kPeer && a.field && a.field_ratio >= 0) {       // the same words in every block: the same decision
-            load_box(bc.box_cur, v->bbox_lo[bc.cur], v->bbox_hi[bc.cur]);
+        if (a.field && a.field_ratio >= 0) {
             const long long cells = (long long)max(0, bc.box_cur[3] - bc.box_cur[0] + 1) * max(0, bc.box_cur[4] - bc.box_cur[1] + 1) * max(0, bc.box_cur[5] - bc.box_cur[2] + 1);
-            bc.use_field = (cells > 0 && (long long)bc.n >= (long long)a.field_ratio * cells) ? 1 : 0;
+            bc.use_field = (cells > 0 && (long long)bc.n >= (long long)a.field_ratio * cells && bc.n >= a.field_min_n) ? 1 : 0;
         }
     };
     auto fetch_after_b1 = [&](int nxt) {
@@ -975,34 +991,38 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         for (int k = 0; k < 6; ++k) s_box[k] = k < 3 ? kGrid : -1;       // merged into the global box before the barrier
         if (bc.gen_hi >= 0) return;                                     // a fall-back pass comes first
         bc.S = v->scan_S; bc.D = v->scan_D; bc.do_compact = v->do_compact; bc.parked = v->parked;
-        if (kPeer) load_box(bc.box_new, v->bbox_lo[nxt], v->bbox_hi[nxt]);
+        if (kPeer) load_box(bc.box_new, v->bbox_lo[nxt], v->bbox_hi[nxt]);     // nxt: the box slot of this step's local deposit
     };
     auto fetch_after_b2 = [&]() { bc.H = min(v->n_holes, v->n_movers); };
-    // the bookkeeping one thread does once an exchange is complete on this rank
-    // ONE thread, once every block has drained its bulk adds and the barrier has fenced them at system scope
-    auto peer_raise_flag = [&](unsigned e) {
-        int lo[3], hi[3];
-        for (int k = 0; k < 3; ++k) { lo[k] = v->bbox_lo[2][k]; hi[k] = v->bbox_hi[2][k]; }
-        peer_signal(a.peer, e, lo, hi);
-    };
-    auto peer_commit = [&](unsigned e) {                     // ONE thread, after peer_raise_flag
-        const int p = (int)(e & 1u);
-        int lo[3], hi[3];
-        for (int k = 0; k < 3; ++k) { lo[k] = v->bbox_lo[2][k]; hi[k] = v->bbox_hi[2][k]; }      // box of this rank's local deposit
-        peer_wait(a.peer, e, lo, hi);                        // every rank's rows have been added into S[p] here
-        for (int k = 0; k < 3; ++k) {
-            v->bbox_lo[p][k] = lo[k]; v->bbox_hi[p][k] = hi[k];          // what S[p] now holds: the union box
-            v->bbox_lo[2][k] = kGrid; v->bbox_hi[2][k] = -1;             // the local grid was emptied on the way out
+    // peer mode.  slot of DevState::bbox that collects the box of the local deposit feeding exchange e (two slots in
+    // alternation: the one of the previous exchange is reset at barrier 1, a whole step after everybody has read it)
+    auto lslot = [](unsigned e) { return 2 + (int)(e & 1u); };
+    // ONE thread per block: wait for exchange e to be complete on this rank, then fetch what the next Poisson step needs.
+    // Block 0 also records the exchange for the host and for the next launch.
+    auto peer_finish = [&](unsigned e) {
+        int ubox[6];
+        peer_wait_all(a.peer, e, ubox);                      // all rows of all ranks have been added into S[e&1]
+        if (blockIdx.x == 0) {
+            const int p = (int)(e & 1u);
+            for (int k = 0; k < 3; ++k) {
+                a.peer.pl->sbox_lo[p][k] = ubox[k]; a.peer.pl->sbox_hi[p][k] = ubox[3 + k];
+                v->bbox_lo[p][k] = ubox[k]; v->bbox_hi[p][k] = ubox[3 + k];
+            }
+            a.peer.pl->xseq = e;
+            v->cur = p;
         }
-        a.peer.pl->xseq = e;
-        v->cur = p;
+        bc.peer_box[0] = ubox[0];                            // (fetch_step_start reads S[e&1]'s box from here, not from PeerLocal:
+        for (int k = 1; k < 6; ++k) bc.peer_box[k] = ubox[k]; //  only block 0 writes that, for the next launch)
+        bc.peer_box_valid = 1;
+        fetch_step_start(e);
     };
+    if (threadIdx.x == 0) bc.peer_box_valid = 0;
     if (kPeer) {
         xe = ld_sys_u32(&a.peer.pl->xseq);
         if (a.initial_deposit) {
-            // particlesToGrid of the first Poisson step for a fresh population: local deposit, push, flags
+            // particlesToGrid of the first Poisson step for a fresh population: local deposit, exchange e
             const unsigned e = xe + 1u;
-            const int p = (int)(e & 1u);
+            const int p = (int)(e & 1u), ls = lslot(e);
             int* mine = a.grid[2];
             const int n = min(ld_volatile_i32(&st->n), a.capacity);
             const int rounded = (n + 31) & ~31;
@@ -1013,21 +1033,25 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
             }
             __syncthreads();
             if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
-                atomicMin(&st->bbox_lo[2][threadIdx.x], s_box[threadIdx.x]);
-                atomicMax(&st->bbox_hi[2][threadIdx.x], s_box[3 + threadIdx.x]);
+                atomicMin(&st->bbox_lo[ls][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[ls][threadIdx.x], s_box[3 + threadIdx.x]);
             }
-            grid_barrier(st, seq, []() {}, [&]() { load_box(bc.box_new, v->bbox_lo[2], v->bbox_hi[2]); fetch_step_start(xe); });
+            grid_barrier(st, seq, [&]() {
+                // the box words of the exchange before this one have been read by everybody long ago (or never written)
+                PeerSync* mysync = a.peer.sync[a.peer.rank];
+                for (int k = 0; k < 3; ++k) { *(volatile int*)&mysync->box_lo[xe & 1u][k] = kGrid; *(volatile int*)&mysync->box_hi[xe & 1u][k] = -1; }
+            }, [&]() { load_box(bc.box_new, v->bbox_lo[ls], v->bbox_hi[ls]); fetch_step_start(xe); });
             peer_add_rows(a.peer, p, a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             // the other summed grid still holds the last exchange of the PREVIOUS population: empty it before
-            // this rank's flag goes up, the peers add the exchange after this one into it
+            // this block arrives, the peers add the exchange after this one into it
             clear_box_rows(a.grid[xe & 1u], bc.box_old, gwarp, nwarp, c.lane);
             peer_add_drain(c.lane);
-            if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
-            grid_barrier(st, seq, [&]() {
-                for (int k = 0; k < 3; ++k) { v->bbox_lo[xe & 1u][k] = kGrid; v->bbox_hi[xe & 1u][k] = -1; }
-                peer_raise_flag(e);
-                peer_commit(e);
-            }, [&]() { fetch_step_start(e); }, true);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                peer_arrive(a.peer, e, bc.box_new);
+                peer_finish(e);
+            }
+            __syncthreads();
             xe = e;
         }
     }
@@ -1043,11 +1067,12 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // Peer mode: grid xe&1 holds the sum over the ranks of exchange xe and is gathered from; this rank
         // deposits into its local grid 2, whose rows all ranks add into each other's grid (xe+1)&1 after barrier 1.
         const int nxt = kPeer ? 2 : (cur + 1) % kRot;
+        const int nbox = kPeer ? lslot(xe + 1u) : nxt;       // DevState::bbox slot that collects the box of this step's deposit
         const int old = kPeer ? (int)(xe & 1u) : (cur + 2) % kRot;
         f.A = a.grid[kPeer ? old : cur];   // gathered from
         f.B = a.grid[nxt];                 // (local) deposit of the next step
         f.F = nullptr;
-        if (!kPeer && bc.use_field) {      // dense plasma: updateGrid over the occupied box first (uniform over the grid)
+        if (bc.use_field) {                // dense plasma: updateGrid over the occupied box first (uniform over the grid)
             field_rows(a.field, f.A, bc.box_cur, a.efc, gwarp, nwarp, c.lane);
             grid_barrier(st, seq, []() {});
             f.F = a.field;
@@ -1109,8 +1134,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 s_pushes = 0; s_dead = 0;
             }
             if (threadIdx.x < 3 && s_box[3 + threadIdx.x] >= 0) {
-                atomicMin(&st->bbox_lo[nxt][threadIdx.x], s_box[threadIdx.x]);
-                atomicMax(&st->bbox_hi[nxt][threadIdx.x], s_box[3 + threadIdx.x]);
+                atomicMin(&st->bbox_lo[nbox][threadIdx.x], s_box[threadIdx.x]);
+                atomicMax(&st->bbox_hi[nbox][threadIdx.x], s_box[3 + threadIdx.x]);
             }
             grid_barrier(st, seq, [&]() {
                 const int unfinished = v->n_unfinished;
@@ -1124,9 +1149,19 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 if (!kPeer) {                                    // the grids change roles; the emptied one has no box
                     for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
                     v->cur = nxt;
+                } else {
+                    // reset what the NEXT step will collect into: the other local-box slot (everybody read it a step ago)
+                    // and the union-box words of the exchange consumed at the start of this step (the peers write them
+                    // again only after they have seen this rank arrive for exchange xe+1, which comes after this barrier)
+                    PeerSync* mysync = a.peer.sync[a.peer.rank];
+                    const int ob = lslot(xe);
+                    for (int k = 0; k < 3; ++k) {
+                        v->bbox_lo[ob][k] = kGrid; v->bbox_hi[ob][k] = -1;
+                        *(volatile int*)&mysync->box_lo[xe & 1u][k] = kGrid; *(volatile int*)&mysync->box_hi[xe & 1u][k] = -1;
+                    }
                 }
             }, [&]() {
-                fetch_after_b1(nxt);
+                fetch_after_b1(nbox);
                 if (!kPeer && bc.gen_hi < 0 && !bc.do_compact) fetch_step_start(0u);     // straight on to the next Poisson step
             });
             const int hi = bc.gen_hi;
@@ -1156,21 +1191,16 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
         // ---- remove_dead_particles (src/pic.cu:320-357), when this step has one: list the holes below the
         // new n and the live electrons above it
         if (compact) compact_scan_body(c.s, st, bc.S, bc.D, a.holes, a.movers, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
-        // peer mode: the bulk adds were issued a whole scan ago; once they are complete this rank's flag goes up
-        if (kPeer) peer_add_drain(c.lane);
+        // peer mode: the bulk adds were issued a whole scan ago; once they are complete this block arrives at every rank
+        if (kPeer) {
+            peer_add_drain(c.lane);
+            __syncthreads();
+            if (threadIdx.x == 0) peer_arrive(a.peer, xe + 1u, bc.box_new);
+        }
         PIC_TRACE(4);
-        grid_barrier(st, seq, [&]() {
-            if (kPeer) {
-                for (int k = 0; k < 3; ++k) { v->bbox_lo[old][k] = kGrid; v->bbox_hi[old][k] = -1; }
-                peer_raise_flag(xe + 1u);
-                if (!compact) peer_commit(xe + 1u);              // nothing left to hide the wait behind
-            }
-        }, [&]() {
-            if (compact) fetch_after_b2();
-            else fetch_step_start(xe + 1u);
-        }, kPeer);
-        PIC_TRACE(5);
         if (compact) {
+            grid_barrier(st, seq, []() {}, [&]() { fetch_after_b2(); });
+            PIC_TRACE(5);
             compact_move_body(c.s, bc.H, a.holes, a.movers);
             PIC_TRACE(6);
             const int parked = bc.parked;
@@ -1189,10 +1219,13 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
                 }
             }
             // ---- barrier 3: the store is dense again
-            grid_barrier(st, seq, [&]() {
-                v->n_holes = 0; v->n_movers = 0;
-                if (kPeer) peer_commit(xe + 1u);
-            }, [&]() { fetch_step_start(xe + 1u); });
+            grid_barrier(st, seq, [&]() { v->n_holes = 0; v->n_movers = 0; }, [&]() { if (!kPeer) fetch_step_start(0u); });
+        }
+        if (kPeer) {
+            // the one cross-GPU barrier of the step: every block of every rank has added its rows into this rank's S
+            if (threadIdx.x == 0) peer_finish(xe + 1u);
+            __syncthreads();
+            if (!compact) PIC_TRACE(5);
         }
         ++xe;
         PIC_TRACE(7);

@@ -4,40 +4,53 @@
 // The reference has no multi-GPU path (device 0 is hard-coded, src/pic.cu:394).  Here every GPU owns
 // a slab of the electrons; the only coupling is the charge grid, whose counts are additive integers
 // (src/grid_operations.cu:25).  Every rank deposits its survivors into a LOCAL grid.  Once the local
-// deposits of a Poisson step are complete, each warp stages one x-row of the occupied box in shared
-// memory and hands the copy engine one bulk REDUCE-ADD (cp.reduce.async.bulk ... .add.s32, TMA) per
+// deposits of a Poisson step are complete (grid barrier 1), each warp stages one x-row of the occupied box in
+// shared memory and hands the copy engine one bulk REDUCE-ADD (cp.reduce.async.bulk ... .add.s32, TMA) per
 // rank: the row is added, by the L2 atomic units at the destination, into the summed grid of EVERY rank
-// (its own included) over NVLink.  The operation is asynchronous -- the warp goes straight on to the
-// compaction while the megabyte is in flight (plain peer loads or stores held the issuing warps for
-// 13 us per step) -- and there is neither a staging copy per rank nor a summing pass: when the flags of
-// all ranks are in, the grid IS the sum.  Integer adds commute, so all ranks hold bit-identical fields
-// and the union of the slabs equals the single-GPU run.  No host round trip, no separate collective
+// (its own included) over NVLink.  There is neither a staging copy per rank nor a summing pass: when every
+// block of every rank has arrived, the grid IS the sum.  Integer adds commute, so all ranks hold bit-identical
+// fields and the union of the slabs equals the single-GPU run.  No host round trip, no separate collective
 // kernel: the whole run stays one cooperative launch per GPU.
 //
+// Synchronisation (round 2): ONE cross-GPU barrier per exchange, counted by remote atomics -- no system-scope
+// grid barrier, no mailbox round trip.  A block that has drained its bulk adds fences at system scope and does
+// one `red.release.sys.add` on the arrival counter of every rank (its own included); a block may go on to the
+// next Poisson step as soon as ITS rank's counter shows that all blocks of all ranks have arrived
+// (`ld.acquire.sys` spin by one thread per block).  The union of the ranks' deposit boxes travels the same way:
+// `red.min` / `red.max` on six words per rank, issued by one block before its arrival.
+//
 // Buffers per rank: L = its local deposit (grid 2), S[0], S[1] = summed grids of even / odd exchanges
-// (grids 0, 1; peers add into them).  Exchange e fills S[e&1]; the step after it gathers from S[e&1] and,
-// once its gathers are done (barrier 1), zeroes it again BEFORE raising the flag of exchange e+1 -- so a
-// peer that sees flag e+1 knows S[(e+2)&1] is clean and may add its exchange e+2 rows at any later time.
+// (grids 0, 1; peers add into them).  Exchange e fills S[e&1]; the step after it gathers from S[e&1] and, once
+// its gathers are done (barrier 1), every block zeroes its rows of it BEFORE arriving for exchange e+1 -- so a
+// peer that has seen all arrivals of exchange e+1 knows S[(e+2)&1] is clean and may add its exchange e+2 rows
+// at any later time.  The same argument covers the box words (reset at barrier 1 of the step that follows
+// their use) and L (a block has read and zeroed its rows of L before it arrives, and nobody deposits into L
+// for the next step before all blocks of the own rank have arrived).
 #pragma once
 
 constexpr int kMaxRanks = 8;
 
-// One message per (exchange parity, source rank), written by the source rank into every peer's mailbox:
-// {box lo packed 3 x 10 bits, box hi likewise, exchange number, 0} in ONE 16-byte store, so the box can
-// never be seen without its sequence number (lo > hi on an axis: empty box).
-struct alignas(16) PeerMsg { uint4 box; };
-struct PeerMailbox { PeerMsg msg[2][kMaxRanks]; };
+// One per rank, in that rank's memory, mapped into every peer's address space (CUDA IPC / peer access).
+// Everything in it is written by remote atomics of the peers (and reset by the owner at a time when no peer can
+// be writing, see above).
+struct PeerSync {
+    alignas(128) unsigned arrive[2];       // per exchange parity: arrivals so far = (exchanges of that parity) x ranks x blocks
+    alignas(128) int box_lo[2][3];         // per exchange parity: union of the ranks' deposit boxes (lo > hi: empty)
+    int box_hi[2][3];
+};
 
-// Survives picb200_upload / init (the exchange counter must never run backwards: peers compare it).
+// Owned by the rank, survives picb200_upload / init (the exchange counter must never run backwards).
 struct PeerLocal {
     unsigned xseq;          // exchanges completed by this rank
-    int error;              // 1: a peer did not show up within the time-out
+    int error;              // (unused since the arrival counters: a time-out traps, see barrier_timeout_abort)
+    int sbox_lo[2][3];      // what S[0], S[1] hold: the union box of the last exchange of that parity
+    int sbox_hi[2][3];
 };
 
 struct PeerArgs {
     int rank, nranks;
-    PeerMailbox* mail[kMaxRanks];   // mailbox of rank r as mapped into this GPU's address space
-    int* sum[kMaxRanks][2];         // summed grids S[0], S[1] of rank r, likewise (own rank: local pointers)
+    PeerSync* sync[kMaxRanks];      // sync block of rank r as mapped into this GPU's address space (own rank: local pointer)
+    int* sum[kMaxRanks][2];         // summed grids S[0], S[1] of rank r, likewise
     PeerLocal* pl;
 };
 
@@ -46,20 +59,16 @@ __device__ __forceinline__ unsigned ld_sys_u32(const unsigned* p) {
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ unsigned long long peer_timer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-__device__ __forceinline__ void st_sys_v4(uint4* p, uint4 v) {
-    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ uint4 ld_sys_v4(const uint4* p) {
-    uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-constexpr unsigned long long kPeerTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;
+__device__ __forceinline__ void red_release_sys_add(unsigned* p, unsigned v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_sys_min(int* p, int v) { asm volatile("red.relaxed.sys.global.min.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void red_sys_max(int* p, int v) { asm volatile("red.relaxed.sys.global.max.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 
 constexpr int kPushSegCells = 64;                       // cells staged per bulk operation (256 B per warp)
 constexpr int kPushStageBytesPerWarp = kPushSegCells * 4;
@@ -71,7 +80,8 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 // All warps of the rank, after the local deposits of this step are complete: add the occupied box of the
 // local grid L into S[p] of every rank, one warp per x-row, and leave L empty for the next step.
 // x-ranges are widened to multiples of 4 cells (bulk operations need 16-byte alignment and size; the extra
-// cells of L are zero).
+// cells of L are zero).  Destinations are visited starting with the next rank, so that at any moment the ranks
+// send to different peers.
 __device__ __forceinline__ void peer_add_rows(const PeerArgs& P, int p, int* __restrict__ L, const int* box /* lo xyz, hi xyz */, int gw, int nw,
                                               int lane, int* stage /* smem, per warp */) {
     if (box[3] < box[0] || box[4] < box[1] || box[5] < box[2]) return;
@@ -94,7 +104,8 @@ __device__ __forceinline__ void peer_add_rows(const PeerArgs& P, int p, int* __r
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> async proxy
             __syncwarp();
             if (lane == 0) {
-                for (int q = 0; q < P.nranks; ++q) {
+                for (int k = 1; k <= P.nranks; ++k) {
+                    const int q = (P.rank + k) % P.nranks;               // (the own grid last)
                     int* dst = P.sum[q][p] + base + x0;
                     asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.s32 [%0], [%1], %2;" ::"l"(dst), "r"(stage_addr), "r"(cells * 4) : "memory");
                 }
@@ -103,38 +114,47 @@ __device__ __forceinline__ void peer_add_rows(const PeerArgs& P, int p, int* __r
         }
     }
 }
-// Every lane that issued bulk operations (lane 0 of each warp): wait until they are complete (the grid
-// barrier that follows fences once per block at system scope).
+// Every lane that issued bulk operations (lane 0 of each warp): wait until they are complete.
 __device__ __forceinline__ void peer_add_drain(int lane) {
     if (lane == 0) bulk_wait_all();
 }
 
-// ONE thread, after every block of this rank has drained its bulk adds and the barrier has fenced them at
-// system scope: tell the peers that this rank's contribution to exchange `e` is complete, and its box.
-__device__ __forceinline__ void peer_signal(const PeerArgs& P, unsigned e, const int* lo, const int* hi) {
-    const bool mine = hi[0] >= lo[0];
-    const uint4 msg = make_uint4(mine ? (unsigned)(lo[0] | (lo[1] << 10) | (lo[2] << 20)) : 0x00100401u,   // empty: lo = 1, hi = 0
-                                 mine ? (unsigned)(hi[0] | (hi[1] << 10) | (hi[2] << 20)) : 0u, e, 0u);
-    __threadfence_system();
-    for (int r = 0; r < P.nranks; ++r)
-        if (r != P.rank) st_sys_v4(&P.mail[r]->msg[e & 1u][P.rank].box, msg);
-}
-// ONE thread: wait until every peer's contribution to exchange `e` has been added into this rank's grid;
-// lo/hi come in as this rank's box and leave as the union over the ranks.
-__device__ __forceinline__ void peer_wait(const PeerArgs& P, unsigned e, int* lo, int* hi) {
-    const unsigned long long t0 = peer_timer_ns();
-    for (int r = 0; r < P.nranks; ++r) {
-        if (r == P.rank) continue;
-        const PeerMsg* m = &P.mail[P.rank]->msg[e & 1u][r];
-        uint4 got = ld_sys_v4(&m->box);
-        while ((int)(got.z - e) < 0) {
-            if (peer_timer_ns() - t0 > kPeerTimeoutNs) { P.pl->error = 1; break; }
-            got = ld_sys_v4(&m->box);
-        }
-        for (int k = 0; k < 3; ++k) {
-            const int pl = (int)((got.x >> (10 * k)) & 1023u), ph = (int)((got.y >> (10 * k)) & 1023u);
-            if (pl <= ph) { lo[k] = min(lo[k], pl); hi[k] = max(hi[k], ph); }
+// ONE thread per block, after a __syncthreads() that follows peer_add_drain() and the block's share of the clearing
+// of the old summed grid: this block's contribution to exchange `e` is complete.  Block 0 also contributes the
+// rank's deposit box to the union (before its own arrival, so that whoever sees the arrival sees the box).
+__device__ __forceinline__ void peer_arrive(const PeerArgs& P, unsigned e, const int* box /* lo xyz, hi xyz of the local deposit */) {
+    const int p = (int)(e & 1u);
+    __threadfence_system();          // the bulk adds this block has waited for, and its plain stores, before the arrival
+    if (blockIdx.x == 0 && box[3] >= box[0] && box[4] >= box[1] && box[5] >= box[2]) {
+        for (int k = 1; k <= P.nranks; ++k) {
+            PeerSync* s = P.sync[(P.rank + k) % P.nranks];
+            for (int a = 0; a < 3; ++a) { red_sys_min(&s->box_lo[p][a], box[a]); red_sys_max(&s->box_hi[p][a], box[3 + a]); }
         }
     }
-    __threadfence_system();
+    for (int k = 1; k <= P.nranks; ++k) red_release_sys_add(&P.sync[(P.rank + k) % P.nranks]->arrive[p], 1u);
+}
+// Arrivals this rank's counter of parity e&1 shows once exchange e is complete everywhere: exchanges 1..e of that
+// parity, each with one arrival per block of every rank (the ranks run equal grids).
+__device__ __forceinline__ unsigned peer_arrival_target(const PeerArgs& P, unsigned e) {
+    const unsigned rounds = (e + (e & 1u)) >> 1;        // e odd: (e+1)/2 odd exchanges so far; e even: e/2 even ones
+    return rounds * (unsigned)P.nranks * gridDim.x;
+}
+// ONE thread per block: wait until every block of every rank has arrived for exchange `e`, i.e. until all rows have
+// been added into this rank's S[e&1]; returns the union box.
+__device__ __forceinline__ void peer_wait_all(const PeerArgs& P, unsigned e, int* box /* out: lo xyz, hi xyz */) {
+    const int p = (int)(e & 1u);
+    const PeerSync* s = P.sync[P.rank];
+    const unsigned target = peer_arrival_target(P, e);
+    if ((int)(ld_acquire_sys_u32(&s->arrive[p]) - target) < 0) {
+        const unsigned long long t0 = timer_ns(), limit = g_barrier_timeout_ns;
+        unsigned spins = 0;
+        while ((int)(ld_acquire_sys_u32(&s->arrive[p]) - target) < 0) {
+            __nanosleep(20);
+            if ((++spins & 255u) == 0u && timer_ns() - t0 > limit) barrier_timeout_abort(3, e);
+        }
+    }
+    for (int a = 0; a < 3; ++a) {
+        box[a] = *(const volatile int*)&s->box_lo[p][a];
+        box[3 + a] = *(const volatile int*)&s->box_hi[p][a];
+    }
 }

@@ -114,3 +114,81 @@ def test_empty_rank_keeps_stepping(engine):
     res = run_ranks(engine, 2, "peer", 0, n, cap, pt, [3])
     assert res[0][0][0]["final_n"] + res[1][0][0]["final_n"] == 1
     assert res[0][0][0]["pushes"] + res[1][0][0]["pushes"] == 15
+
+
+@pytest.mark.parametrize("k", [2])
+def test_second_population_on_the_same_ranks(engine, k):
+    """Two populations one after the other on the SAME simulations (what bench.py does between timed runs): the summed
+    grid that still holds the last exchange of the first population must be emptied before the second one uses it, and
+    the exchange counters carry on.  k slabs == one GPU for both populations."""
+    need_gpus(engine, k)
+    n, pt, cap = 48000, 10, 960000
+    rng = np.random.default_rng(11)
+    pops = []
+    for shift in (0.0, 0.07):
+        pos = (rng.uniform(2.45, 2.65, size=(3, n)) + shift).astype(np.float32)
+        vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)
+        pops.append((pos, vel))
+    singles = []
+    with engine.Sim(mode=0, capacity=cap, poisson_timestep=pt, poisson_steps=8) as one:
+        for pos, vel in pops:
+            one.upload(*pos, *vel)
+            one.run_steps(3)
+            one.run_steps(2)
+            singles.append((one.summary(), one.download().sorted_by_id()))
+    handles = [None] * k
+    out = [[] for _ in range(k)]
+    err = []
+    bar = threading.Barrier(k)
+
+    def work(r):
+        try:
+            sim = engine.Sim(mode=0, capacity=cap // k, poisson_timestep=pt, poisson_steps=8, device=r, rank=r, nranks=k)
+            handles[r] = sim.peer_export()
+            bar.wait()
+            sim.peer_connect(handles)
+            lo, hi = n * r // k, n * (r + 1) // k
+            for pos, vel in pops:
+                sim.upload(*[a[lo:hi] for a in pos], *[a[lo:hi] for a in vel], id=np.arange(lo, hi, dtype=np.uint64))
+                bar.wait()
+                sim.run_steps(3)
+                sim.run_steps(2)
+                out[r].append((sim.summary(), sim.download()))
+                bar.wait()
+            sim.close()
+        except Exception as e:  # noqa: BLE001
+            err.append((r, repr(e)))
+            bar.abort()
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(k)]
+    [t.start() for t in th]
+    [t.join(timeout=300) for t in th]
+    assert not err, err
+    for j, (s1, d1) in enumerate(singles):
+        sums = [out[r][j][0] for r in range(k)]
+        assert sum(s["final_n"] for s in sums) == s1["final_n"] and sum(s["pushes"] for s in sums) == s1["pushes"], j
+        assert sum(s["total_added"] for s in sums) == s1["total_added"] and s1["total_added"] > 500
+        u = union_sorted([out[r][j][1] for r in range(k)])
+        assert np.array_equal(u["id"], d1.id), j
+        for f in F32:
+            assert np.array_equal(u[f], getattr(d1, f)), (j, f)
+
+
+def test_large_slabs_use_the_per_cell_field_in_peer_mode(engine, monkeypatch):
+    """Peer mode with the per-cell field path forced on (PICB200_FIELD_MIN_N=0, ratio 0) and off: both equal one GPU."""
+    need_gpus(engine, 2)
+    n, pt, cap, P = 64000, 10, 1024000, 6
+    with engine.Sim(mode=0, capacity=cap, poisson_timestep=pt, poisson_steps=P) as one:
+        one.init_uniform(n)
+        one.run_steps(P)
+        s1, d1 = one.summary(), one.download().sorted_by_id()
+    for ratio in ("0", "-1"):
+        monkeypatch.setenv("PICB200_FIELD_MIN_N", "0")
+        monkeypatch.setenv("PICB200_FIELD_RATIO", ratio)
+        res = run_ranks(engine, 2, "peer", 0, n, cap, pt, [2, 4])
+        sums = [res[r][1][0] for r in range(2)]
+        assert sum(s["final_n"] for s in sums) == s1["final_n"] and sum(s["pushes"] for s in sums) == s1["pushes"]
+        u = union_sorted([res[r][1][1] for r in range(2)])
+        assert np.array_equal(u["id"], d1.id)
+        for f in F32:
+            assert np.array_equal(u[f], getattr(d1, f)), (ratio, f)

@@ -18,7 +18,7 @@ if tl.shape[0]:
     rows = [("own chunks of warp 0 (0->1)", 0, 1), ("wait for block's other warps (1->2)", 1, 2), ("barrier 1 + bookkeeping (2->3)", 2, 3)]
     if tl[:, :, 5].min() > 0:      # peer mode: the exchange follows barrier 1 in every step
         rows += [("peer: push rows to the peers (3->11)", 3, 11), ("peer: clear own old grid (11->8)", 11, 8), ("peer: drain bulk adds (8->4)", 8, 4),
-                 ("peer: barrier 2 = flag up + wait for peers (4->5)", 4, 5)]
+                 ("peer: arrive at every rank + wait for all blocks of all ranks (4->5)", 4, 5)]
     for nm, a_, b_ in rows:
         d = (tl[:, :, b_] - tl[:, :, a_]) / 1e3
         print(f"  [no compaction] {nm:50s} mean {d.mean():7.1f}  min-block {np.median(d.min(1)):7.1f}  max-block {np.median(d.max(1)):7.1f}")
