@@ -166,6 +166,9 @@ int picb200_charge_bbox(picb200_sim* sim, int32_t lo[3], int32_t hi[3]);
 int picb200_dev_philox(int32_t device, int64_t n, const uint32_t* ctr, const uint32_t* key, uint32_t* out);
 /* energyToIndex (src/cross_section.cu:32-35) for n fp32 energies */
 int picb200_dev_energy_index(int32_t device, int64_t n, const float* energy, int32_t* out);
+/* energyToIndex on the device for every stride-th non-negative fp32 bit pattern (stride 1: all 2^31, incl. +inf and NaNs),
+ * compared with a bisection of the exact bin-edge table; returns the number of mismatches and one offending bit pattern */
+int picb200_dev_energy_index_sweep(int32_t device, uint32_t stride, int64_t* mismatches, uint32_t* first_bad_bits);
 /* host-side loader (src/cross_section.cu:3-28): returns rows read, -1 if the file cannot be opened */
 int picb200_load_table(const char* path, float* rows2);
 

@@ -110,6 +110,7 @@ SIGNATURES = {
     "picb200_charge_bbox": (C.c_int, [_sim, _ip, _ip]),
     "picb200_dev_philox": (C.c_int, [C.c_int32, C.c_int64, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "picb200_dev_energy_index": (C.c_int, [C.c_int32, C.c_int64, _fp, _ip]),
+    "picb200_dev_energy_index_sweep": (C.c_int, [C.c_int32, C.c_uint32, C.POINTER(C.c_int64), C.POINTER(C.c_uint32)]),
     "picb200_load_table": (C.c_int, [C.c_char_p, _fp]),
     "picb200_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "picb200_peer_export": (C.c_int, [_sim, C.c_void_p]),
@@ -376,6 +377,13 @@ def dev_energy_index(energy, device=-1):
     out = np.empty(e.shape, dtype=np.int32)
     _check(lib.picb200_dev_energy_index(device, e.size, _ptr(e, _fp), _ptr(out, _ip)))
     return out
+
+
+def dev_energy_index_sweep(stride=1, device=-1):
+    """(mismatches, bits of one offender) of the device's energy_index over every stride-th non-negative fp32 bit pattern."""
+    bad, first = C.c_int64(0), C.c_uint32(0)
+    _check(lib.picb200_dev_energy_index_sweep(device, stride, C.byref(bad), C.byref(first)))
+    return bad.value, first.value
 
 
 def load_table(path=None):

@@ -127,11 +127,28 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-        uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
-        uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        // one 32 x 32 -> 64 multiply per word pair (IMAD.WIDE.U32), not a high and a low multiply each
+        const unsigned long long p0 = (unsigned long long)M0 * c.x, p1 = (unsigned long long)M1 * c.z;
+        c = make_uint4((uint32_t)(p1 >> 32) ^ c.y ^ k.x, (uint32_t)p1, (uint32_t)(p0 >> 32) ^ c.w ^ k.y, (uint32_t)p0);
         k.x += W0;
         k.y += W1;
+    }
+    return c;
+}
+// The same generator with its key schedule (round r uses key + r * Weyl constant) worked out once on the host and read
+// from the kernel's parameter bank: two multiplies and two three-way XORs per round, nothing else.
+struct PhiloxKeys { uint2 k[10]; };
+inline PhiloxKeys philox_round_keys(uint2 key) {
+    PhiloxKeys ks;
+    for (int r = 0; r < 10; ++r) { ks.k[r] = key; key.x += 0x9E3779B9u; key.y += 0xBB67AE85u; }
+    return ks;
+}
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, const PhiloxKeys& ks) {
+    constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const unsigned long long p0 = (unsigned long long)M0 * c.x, p1 = (unsigned long long)M1 * c.z;
+        c = make_uint4((uint32_t)(p1 >> 32) ^ c.y ^ ks.k[r].x, (uint32_t)p1, (uint32_t)(p0 >> 32) ^ c.w ^ ks.k[r].y, (uint32_t)p0);
     }
     return c;
 }
@@ -148,25 +165,31 @@ __device__ __forceinline__ unsigned long long child_id(unsigned long long parent
     return z | 0x8000000000000000ull;
 }
 
-// energyToIndex (src/cross_section.cu:32-35) without the fp64 log10: a cubic estimate of
-// s = (log10(E)+6)*10000/22 (|error| < 0.15), rounded to the nearest bin boundary j, then one
-// shared-memory probe of the exact boundary energy: edge[j] is the smallest fp32 E whose
-// reference index (double formula) is >= j.  The result equals the reference formula for every
-// fp32 E (verified exhaustively on the CPU by tests/tools/check_energy_index.cpp).
+// energyToIndex (src/cross_section.cu:32-35) without the fp64 log10: an estimate of
+// s = (log10(E)+6)*10000/22 from the SFU's log2 (lg2.approx: absolute error of s below 0.01, where 0.5 would do),
+// rounded to the nearest bin boundary j, then one shared-memory probe of the exact boundary energy: edge[j] is the
+// smallest fp32 E whose reference index (double formula) is >= j.  j is clamped to [0, kRows-1], so an energy beyond
+// the last boundary needs no second clamp; E = 0 and subnormals (flushed) give lg2 = -inf -> j = 0; a NaN energy
+// gives j = cvt(NaN) = 0 and fails the comparison -> 0, the reference's saturating conversion.
+// The result equals the reference formula for EVERY fp32 E: the edge table is checked against the double formula on
+// the CPU (tests/tools/check_energy_index.cpp), the estimate-and-probe against a bisection of that table on the
+// device (k_sweep_energy_index, all 2^31 non-negative bit patterns).
 __device__ __forceinline__ int energy_index(float e, const float* __restrict__ s_edge) {
-    const uint32_t b = __float_as_uint(e);
-    const int ex = (int)(b >> 23) - 127;
-    const float m = __uint_as_float((b & 0x007fffffu) | 0x3f800000u);
-    float p = __fmaf_rn(m, 0.155445858836174f, -1.0392581224441528f);
-    p = __fmaf_rn(p, m, 3.0294783115386963f);
-    p = __fmaf_rn(p, m, -2.1449406147003174f);
-    const float lg = __int2float_rn(ex) + p;                                   // ~log2(E)
+    float lg;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(e));
     const float s = __fmaf_rn(lg, 136.83181621090054f, 2727.2727272727275f);   // *log10(2)*1e4/22, +6e4/22
-    int j = __float2int_rn(s);
-    j = max(0, min(j, kRows));
-    int idx = j - ((e < s_edge[j]) ? 1 : 0);
-    idx = min(idx, kRows - 1);
-    return (e != e) ? 0 : idx;      // NaN: the reference's saturating cvt gives 0
+    const int j = max(0, min(__float2int_rn(s), kRows - 1));
+    return j - ((e < s_edge[j]) ? 1 : 0);
+}
+// the same index by bisection of the edge table (no estimate involved): the yardstick of the device-side sweep
+__device__ __forceinline__ int energy_index_bisect(float e, const float* __restrict__ edge) {
+    if (e != e) return 0;
+    int lo = 0, hi = kRows;                // invariant: edge[lo] <= e (edge[0] = 0 <= e for e >= 0), edge[hi] > e or hi == kRows
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (e >= edge[mid]) lo = mid; else hi = mid;
+    }
+    return lo;
 }
 
 // cell index of a coordinate: int(pos / cell_size), double divide, C truncation
@@ -525,6 +548,18 @@ __global__ void k_test_philox(long long n, const uint32_t* ctr, uint2 key, uint3
         uint4 r = philox4x32_10(make_uint4(ctr[4 * i], ctr[4 * i + 1], ctr[4 * i + 2], ctr[4 * i + 3]), key);
         out[4 * i] = r.x; out[4 * i + 1] = r.y; out[4 * i + 2] = r.z; out[4 * i + 3] = r.w;
     }
+}
+// every stride-th non-negative fp32 bit pattern (0 .. 0x7fffffff: zero, subnormals, normals, +inf, NaNs): energy_index
+// against the bisection of the same edge table; out[0] = mismatches, out[1] = bits of the first one seen
+__global__ void k_sweep_energy_index(unsigned stride, const float* tables, unsigned long long* out) {
+    const float* edge = reinterpret_cast<const float*>(reinterpret_cast<const unsigned char*>(tables) + kThrBytes);
+    unsigned long long bad = 0;
+    for (unsigned long long b = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * stride; b <= 0x7fffffffull;
+         b += (unsigned long long)gridDim.x * blockDim.x * stride) {
+        const float e = __uint_as_float((unsigned)b);
+        if (energy_index(e, edge) != energy_index_bisect(e, edge)) { ++bad; out[1] = b; }
+    }
+    if (bad) atomicAdd(out, bad);
 }
 __global__ void k_test_energy_index(long long n, const float* e, const float* tables, int* out) {
     const float* edge = reinterpret_cast<const float*>(reinterpret_cast<const unsigned char*>(tables) + kThrBytes);

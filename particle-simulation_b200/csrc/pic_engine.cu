@@ -693,7 +693,7 @@ int Sim::fused_steps(int steps) {
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy,
                     std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt)),
-                    (peer || cfg.nranks == 1) ? field : nullptr, field_ratio, field_min_n, getenv("PICB200_TEST_DESERT") ? 1 : 0};
+                    (peer || cfg.nranks == 1) ? field : nullptr, field_ratio, field_min_n, getenv("PICB200_TEST_DESERT") ? 1 : 0, philox_round_keys(seed)};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)
         const char* trace_path = getenv("PICB200_TRACE");
@@ -1068,6 +1068,26 @@ int picb200_dev_energy_index(int32_t device, int64_t n, const float* energy, int
     cudaError_t e = cudaMemcpy(out, d_o, (size_t)n * 4, cudaMemcpyDeviceToHost);
     cudaFree(d_t); cudaFree(d_e); cudaFree(d_o);
     CK(e, "Energy index test");
+    return 0;
+}
+int picb200_dev_energy_index_sweep(int32_t device, uint32_t stride, int64_t* mismatches, uint32_t* first_bad_bits) {
+    if (picb200_device_count() == 0) return fail("no CUDA device", "Energy index sweep");
+    if (device >= 0) CK(cudaSetDevice(device), "Set device");
+    std::vector<unsigned char> img((size_t)kTableSmemBytes, 0);
+    build_energy_edges(reinterpret_cast<float*>(img.data() + kThrBytes));
+    float* d_t = nullptr;
+    unsigned long long* d_o = nullptr;
+    unsigned long long h[2] = {0, 0};
+    CK(cudaMalloc(&d_t, (size_t)kTableSmemBytes), "Energy index sweep");
+    CK(cudaMalloc(&d_o, sizeof(h)), "Energy index sweep");
+    CK(cudaMemcpy(d_t, img.data(), (size_t)kTableSmemBytes, cudaMemcpyHostToDevice), "Energy index sweep");
+    CK(cudaMemset(d_o, 0, sizeof(h)), "Energy index sweep");
+    k_sweep_energy_index<<<148 * 8, 256>>>(stride ? stride : 1u, d_t, d_o);
+    cudaError_t e = cudaMemcpy(h, d_o, sizeof(h), cudaMemcpyDeviceToHost);
+    cudaFree(d_t); cudaFree(d_o);
+    CK(e, "Energy index sweep");
+    if (mismatches) *mismatches = (int64_t)h[0];
+    if (first_bad_bits) *first_bad_bits = (uint32_t)h[1];
     return 0;
 }
 int picb200_load_table(const char* path, float* rows2) {

@@ -60,6 +60,7 @@ struct MoverCtx {
     int* pool;           // fused kernel: free slots this warp has come across in the current Poisson step (shared memory)
     unsigned g0;
     uint2 seed;
+    const PhiloxKeys* keys;   // fused kernel: the round keys of `seed`, in the kernel's parameter bank
 };
 
 // Reserve `count` consecutive slots of the global store: one atomic per call, honouring the
@@ -405,6 +406,7 @@ struct FusedArgs {
     int field_ratio;             // a Poisson step computes the field per cell when n >= field_ratio * cells of the occupied box (< 0: never)
     int field_min_n;             // ... and the rank holds at least this many electrons (peer mode: the pass costs a barrier per rank)
     int test_desert;             // PICB200_TEST_DESERT=1 (tests): the last block leaves the kernel at once -> the grid barrier must time out
+    PhiloxKeys keys;             // philox_round_keys(seed)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -422,14 +424,14 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // (bnd[0] = -inf, bnd[512] = +inf, built on the host; checked for every fp32 in the domain by
 // tests/tools/check_cell_index.cpp).  Clamped to the grid like cell_of().
 constexpr int kBndBytes = (kGrid + 1) * 4;
-// PIC_CELL_ONE_PROBE (off; prepared for the next round, not yet measured on a GPU): the estimate is taken with a
-// multiplier four ulps below 100, which makes it the true index or one less for every fp32 in the domain -- never
-// more -- so ONE probe upwards settles it (three instructions less per coordinate, six coordinates per electron
-// and Poisson step).  Checked against the reference formula for every fp32 with |x| <= 8 by
-// tests/tools/check_cell_index.cpp -DONE_PROBE.
+// The estimate is taken with a multiplier four ulps below 100, which makes it the true index or one less for every fp32
+// in the domain -- never more -- so ONE probe upwards settles it (round 1 estimated with 100.0f and probed both ways:
+// three instructions more per coordinate, six coordinates per electron and Poisson step; -DPIC_CELL_TWO_PROBES keeps
+// that form).  Both are checked against the reference formula for every fp32 with |x| <= 8 by
+// tests/tools/check_cell_index.cpp (-DONE_PROBE: this one).
 constexpr float kCellScaleLow = 99.999969482421875f;       // 0x42C7FFFC = 100 - 4 ulp
 __device__ __forceinline__ int cell_of_fast(float p, const float* __restrict__ bnd) {
-#ifdef PIC_CELL_ONE_PROBE
+#ifndef PIC_CELL_TWO_PROBES
     int k = __float2int_rz(__fmul_rn(p, kCellScaleLow));
     k = max(0, min(k, kGrid - 1));
     k += (p >= bnd[k + 1]) ? 1 : 0;
@@ -588,7 +590,7 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
     for (int t = t_first; t <= c.pt; ++t) {
         const unsigned g = c.g0 + (unsigned)t;
         if (t == t_first || (g & 3u) == 0u || (kAdopt && refresh)) {         // warp-uniform
-            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), c.seed);
+            rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), *c.keys);
             refresh = false;
         }
         const bool act = kStaged ? (alive & (t > tb)) : alive;
@@ -907,7 +909,7 @@ static_assert(kSS >= 32 && kSS <= 64, "stage_select_earliest handles up to 64 en
 // kAdopt: the chunks use the adopting step loop (lockstep_push); the host picks it for poisson_timestep >= kAdoptMinSteps --
 // it carries more state through every step and only pays when lanes die out long before the Poisson step ends.
 template <bool kPeer, bool kAdopt>
-__global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
+__global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant__ FusedArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_box[6];
     __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
@@ -937,6 +939,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(FusedArgs a) {
     c.stepwise = 0;
     c.adopt_min = a.adopt_min;
     c.seed = a.seed;
+    c.keys = &a.keys;
     FusedCtx f;
     f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
     f.s_box = s_box;

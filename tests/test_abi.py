@@ -60,9 +60,10 @@ def test_edge_table_is_the_reference_formula(engine, oracle):
 
 
 def test_device_energy_index_formula_emulated_on_cpu(engine, tmp_path):
-    """The device's estimate-and-probe index equals the reference formula on a strided sweep of
-    all non-negative fp32 values plus +-3 ulp around every bin edge (the exhaustive sweep,
-    stride 1, passes too: 2 147 553 641 values, 0 mismatches)."""
+    """The exact bin-edge table the device probes reproduces the reference formula on a strided sweep of
+    all non-negative fp32 values plus +-3 ulp around every bin edge (the exhaustive sweep, stride 1, passes
+    too: 2 147 553 641 values, 0 mismatches); the device's SFU estimate is swept on the device
+    (tests/test_parity_gpu.py::test_energy_index_exhaustive_on_device)."""
     exe = tmp_path / "cei"
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     subprocess.run([cxx, "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fopenmp", "-o", str(exe),
@@ -76,7 +77,7 @@ def test_device_energy_index_formula_emulated_on_cpu(engine, tmp_path):
 def test_device_cell_index_formula_emulated_on_cpu(engine, tmp_path, variant):
     """cell_of_fast() (one fp32 multiply + a probe of exact cell boundaries) equals the reference's
     int(double(pos)/1e-2) (src/grid_operations.cu:21-23) for EVERY fp32 with |x| <= 8 (2.2e9 values);
-    -DONE_PROBE: the single-probe form prepared behind PIC_CELL_ONE_PROBE."""
+    -DONE_PROBE: the single-probe form the kernels use (round 1's two-probe form stays behind -DPIC_CELL_TWO_PROBES)."""
     exe = tmp_path / "cci"
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     subprocess.run([cxx, "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fopenmp", *variant, "-o", str(exe),

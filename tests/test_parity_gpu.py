@@ -70,6 +70,13 @@ def test_energy_index_on_device(engine, oracle):
     assert np.array_equal(got, exp)
 
 
+def test_energy_index_exhaustive_on_device(engine):
+    """energy_index() (SFU lg2 estimate + one probe of the exact edge table) against a bisection of the table for EVERY
+    non-negative fp32 bit pattern -- 2^31 values incl. zero, subnormals, +inf and all NaNs -- on the device."""
+    bad, first = engine.dev_energy_index_sweep(stride=1)
+    assert bad == 0, (bad, hex(first))
+
+
 # ------------------------------------------------------------------------------------------
 # kernels, one phase at a time
 # ------------------------------------------------------------------------------------------

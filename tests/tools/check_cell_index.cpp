@@ -18,14 +18,14 @@ static inline int ref_cell(float x) {                      // cell_of(): the ref
 }
 
 #ifdef ONE_PROBE
-static inline int dev_cell(float x, const float* bnd) {    // cell_of_fast() under PIC_CELL_ONE_PROBE, operation for operation
+static inline int dev_cell(float x, const float* bnd) {    // cell_of_fast() (the default single-probe form), operation for operation
     int k = (int)(x * 99.999969482421875f);                // kCellScaleLow = 100 - 4 ulp: the estimate is never above the index
     k = k < 0 ? 0 : (k > kGrid - 1 ? kGrid - 1 : k);
     k += (x >= bnd[k + 1]) ? 1 : 0;
     return k;
 }
 #else
-static inline int dev_cell(float x, const float* bnd) {    // cell_of_fast(), operation for operation
+static inline int dev_cell(float x, const float* bnd) {    // cell_of_fast() under -DPIC_CELL_TWO_PROBES, operation for operation
     int k = (int)(x * 100.0f);                             // __float2int_rz(__fmul_rn(p, 100.0f)); |x| < 8 here, no saturation
     k = k < 0 ? 0 : (k > kGrid - 1 ? kGrid - 1 : k);
     k -= (x < bnd[k]) ? 1 : 0;
