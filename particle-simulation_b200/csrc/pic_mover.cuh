@@ -445,23 +445,40 @@ __device__ __forceinline__ int cell_of_fast(float p, const float* __restrict__ b
 #endif
 }
 
+// Atomics written as the single instruction they are: nvcc wraps an atomicAdd whose address it cannot prove distinct
+// per lane in its own warp-aggregation code (vote, leader election, popc, shuffle: ~15 instructions around one
+// ATOMS/ATOMG), which is pure overhead where the caller has already elected one lane.
+__device__ __forceinline__ int smem_fetch_add(int* p, int v) {
+    int old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void red_global_add(int* p, int v) { asm volatile("red.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
 // NGP deposit of the active lanes with warp-level pre-reduction (lanes that hit the same cell
-// are merged into one red.global.add) and a block-level bounding box in shared memory.
+// are merged into one red.global.add) and a block-level bounding box in shared memory
+// (s_box: lo xyz, hi xyz, 16-byte aligned).  The box only grows; nearly every chunk lies inside what the block
+// has already seen, so the warp first tests its cells against the box as it stands (a stale read errs on the safe
+// side) and reduces its own extent only when some lane falls outside.
 __device__ __forceinline__ void deposit_lanes(int* __restrict__ grid, bool active, int ix, int iy, int iz, int lane, int* s_box) {
     const unsigned cell = active ? (unsigned)cell_index(ix, iy, iz) : (0xffffffffu - (unsigned)lane);
     const unsigned peers = __match_any_sync(kFull, cell);
-    if (active && lane == __ffs(peers) - 1) atomicAdd(grid + cell, __popc(peers));
-    const int lx = __reduce_min_sync(kFull, active ? ix : kGrid), ly = __reduce_min_sync(kFull, active ? iy : kGrid),
-              lz = __reduce_min_sync(kFull, active ? iz : kGrid);
-    const int hx = __reduce_max_sync(kFull, active ? ix : -1), hy = __reduce_max_sync(kFull, active ? iy : -1),
-              hz = __reduce_max_sync(kFull, active ? iz : -1);
-    if (lane == 0 && hx >= 0) {
-        if (lx < s_box[0]) atomicMin(&s_box[0], lx);
-        if (ly < s_box[1]) atomicMin(&s_box[1], ly);
-        if (lz < s_box[2]) atomicMin(&s_box[2], lz);
-        if (hx > s_box[3]) atomicMax(&s_box[3], hx);
-        if (hy > s_box[4]) atomicMax(&s_box[4], hy);
-        if (hz > s_box[5]) atomicMax(&s_box[5], hz);
+    if (active && lane == __ffs(peers) - 1) red_global_add(grid + cell, __popc(peers));
+    int4 b0;                                                                 // lo x y z, hi x
+    int2 b1;                                                                 // hi y z
+    const unsigned box_addr = (unsigned)__cvta_generic_to_shared(s_box);
+    asm volatile("ld.volatile.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(b0.x), "=r"(b0.y), "=r"(b0.z), "=r"(b0.w) : "r"(box_addr));
+    asm volatile("ld.volatile.shared.v2.s32 {%0,%1}, [%2];" : "=r"(b1.x), "=r"(b1.y) : "r"(box_addr + 16u));
+    const bool outside = active & ((ix < b0.x) | (iy < b0.y) | (iz < b0.z) | (ix > b0.w) | (iy > b1.x) | (iz > b1.y));
+    if (__any_sync(kFull, outside)) {
+        const int lx = __reduce_min_sync(kFull, active ? ix : kGrid), ly = __reduce_min_sync(kFull, active ? iy : kGrid),
+                  lz = __reduce_min_sync(kFull, active ? iz : kGrid);
+        const int hx = __reduce_max_sync(kFull, active ? ix : -1), hy = __reduce_max_sync(kFull, active ? iy : -1),
+                  hz = __reduce_max_sync(kFull, active ? iz : -1);
+        if (lane == 0) {
+            atomicMin(&s_box[0], lx); atomicMin(&s_box[1], ly); atomicMin(&s_box[2], lz);
+            atomicMax(&s_box[3], hx); atomicMax(&s_box[4], hy); atomicMax(&s_box[5], hz);
+        }
     }
 }
 
@@ -911,7 +928,7 @@ static_assert(kSS >= 32 && kSS <= 64, "stage_select_earliest handles up to 64 en
 template <bool kPeer, bool kAdopt>
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant__ FusedArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ int s_box[6];
+    __shared__ __align__(16) int s_box[8];     // lo xyz, hi xyz of this block's deposits (deposit_lanes reads it as int4 + int2)
     __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
     __shared__ unsigned long long s_pushes;
     __shared__ int s_dead;
@@ -1103,7 +1120,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
         for (bool more = true; more || staged;) {
             if (more) {
                 int k = 0;
-                if (c.lane == 0) k = atomicAdd(&s_ticket, 1);
+                if (c.lane == 0) k = smem_fetch_add(&s_ticket, 1);
                 const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
                 more = chunk < chunks;
                 if (more) fused_chunk_fast<kAdopt>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);

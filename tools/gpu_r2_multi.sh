@@ -1,9 +1,11 @@
 #!/bin/bash
-# N GPUs of one box: multi-GPU parity tests, bench under torchrun (with its self-check), phase trace of the peer exchange.
+# N GPUs of one box: the whole GPU suite (multi-GPU parity included), bench under torchrun (with its self-check),
+# phase trace of the peer exchange, single-GPU bench on the same box.
 O=gpurun_out; mkdir -p $O
 N=${1:-2}
 nvidia-smi -L | head -8
-timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -x -q 2>&1 | tail -15
+if [ "${FULL_SUITE:-1}" = "1" ]; then timeout 1200 python -m pytest tests -m gpu -q > $O/pytest_gpu_n$N.log 2>&1; echo "pytest rc=$?"; tail -6 $O/pytest_gpu_n$N.log | cut -c1-300
+else timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -x -q 2>&1 | tail -15; fi
 PICB200_BENCH_NO_CFG4=${NO_CFG4:-0} timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 5 --warmup 3 > $O/bench_n$N.json 2> $O/bench_n$N.err; echo "bench N=$N rc=$?"
 tail -c 1500 $O/bench_n$N.err; python - <<PY
 import json
@@ -19,3 +21,5 @@ PICB200_BENCH_NO_CPU=1 PICB200_BENCH_NO_CFG4=1 timeout 600 python bench.py --ste
 import json
 d=json.loads(open("$O/bench_n1.json").read().strip().splitlines()[-1]); print("N=1 value %.4g ms/step %.3f" % (d["value"], d["ms_per_step"]))
 PY
+for a in "30 0 10000000 10 256 100000000 100 1" "30 0 10000000 10 256 100000000 100 10" "30 0 10000000 10 256 100000000 100 100"; do
+  echo "$a :: $(PICB200_PRINT_PUSHES=1 ./run $a 2>&1 | grep -E 'GPU time|pushes' | tr '\n' ' ')"; done
