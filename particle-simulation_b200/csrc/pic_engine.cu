@@ -477,19 +477,19 @@ int Sim::peer_connect(const void* handles) {
     }
     // connect before the first population is created (the grids are still all-zero then)
     if (charge_valid) return fail("picb200_peer_connect must precede the first Poisson step", "Peer setup");
+    pa.debug = getenv("PICB200_PEER_DEBUG") ? atoi(getenv("PICB200_PEER_DEBUG")) : 0;
     peer_connected = true;
     return 0;
 }
 
 int Sim::sync_state() {
-    CK(cudaMemcpyAsync(h_st, st, sizeof(DevState), cudaMemcpyDeviceToHost, stream), "State readback");
-    if (pl) CK(cudaMemcpyAsync(h_pl, pl, sizeof(PeerLocal), cudaMemcpyDeviceToHost, stream), "State readback");
-    {
-        const cudaError_t e = cudaStreamSynchronize(stream);
-        if (e != cudaSuccess) {                  // a kernel died: say which barrier gave up, if one did (barrier_timeout_abort)
-            const std::string why = abort_message(device);
-            return fail(why.empty() ? std::string(cudaGetErrorString(e)) : why + " [" + cudaGetErrorString(e) + "]", why.empty() ? "State readback" : "Mobility steps");
-        }
+    // a kernel that died makes whichever call comes next fail: say which barrier gave up, if one did (barrier_timeout_abort)
+    cudaError_t e = cudaMemcpyAsync(h_st, st, sizeof(DevState), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess && pl) e = cudaMemcpyAsync(h_pl, pl, sizeof(PeerLocal), cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) {
+        const std::string why = abort_message(device);
+        return fail(why.empty() ? std::string(cudaGetErrorString(e)) : why + " [" + cudaGetErrorString(e) + "]", why.empty() ? "State readback" : "Mobility steps");
     }
     cur = h_st->cur;
     if (h_st->error == 2) return fail("more children waited for a compaction than the parking area holds", "Mobility phase");

@@ -52,6 +52,7 @@ struct PeerArgs {
     PeerSync* sync[kMaxRanks];      // sync block of rank r as mapped into this GPU's address space (own rank: local pointer)
     int* sum[kMaxRanks][2];         // summed grids S[0], S[1] of rank r, likewise
     PeerLocal* pl;
+    int debug;                      // PICB200_PEER_DEBUG (timing experiments only, results are wrong): 1 = skip the add into the own grid, 2 = skip the adds into the peers' grids
 };
 
 __device__ __forceinline__ unsigned ld_sys_u32(const unsigned* p) {
@@ -106,6 +107,7 @@ __device__ __forceinline__ void peer_add_rows(const PeerArgs& P, int p, int* __r
             if (lane == 0) {
                 for (int k = 1; k <= P.nranks; ++k) {
                     const int q = (P.rank + k) % P.nranks;               // (the own grid last)
+                    if (P.debug && ((q == P.rank) ? (P.debug & 1) : (P.debug & 2))) continue;
                     int* dst = P.sum[q][p] + base + x0;
                     asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.s32 [%0], [%1], %2;" ::"l"(dst), "r"(stage_addr), "r"(cells * 4) : "memory");
                 }

@@ -91,8 +91,12 @@ static int run_impl(const picb200_config* cfg_in, picb200_summary* out, picb200_
             if (failed) break;
             const size_t n_log = (size_t)std::max(1, std::min(cfg.poisson_steps, s.log_len));
             std::vector<StepLog> lg(n_log);
-            if (cudaMemcpyAsync(lg.data(), s.log, sizeof(StepLog) * n_log, cudaMemcpyDeviceToHost, s.stream) != cudaSuccess) { fail("log readback", "Mobility steps"); break; }
-            if (s.sync_state()) break;                           // (keeps the message: e.g. a grid barrier that timed out)
+            // (a kernel that died -- e.g. a grid barrier that timed out -- makes either call fail: sync_state has the message)
+            if (cudaMemcpyAsync(lg.data(), s.log, sizeof(StepLog) * n_log, cudaMemcpyDeviceToHost, s.stream) != cudaSuccess) {
+                if (!s.sync_state()) fail("log readback", "Mobility steps");
+                break;
+            }
+            if (s.sync_state()) break;
             if (say) {
                 for (int t = t_begin; t < s.h_st->poisson_index && (size_t)t < n_log; ++t) {
                     if (lg[(size_t)t].n_after_mobility >= cfg.capacity) printf("\n\nOVERFLOW FROM ADDING PARTICLES\n\n\n");
