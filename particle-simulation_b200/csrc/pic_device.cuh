@@ -29,6 +29,14 @@ constexpr int kThrBytes = kRows * 8;
 constexpr int kEdgeBytes = (kRows + 1) * 4;
 constexpr int kTableSmemBytes = ((kThrBytes + kEdgeBytes + 15) / 16) * 16;
 
+// The streaming instantiation of the fused kernel (small poisson_timestep, HBM-side) keeps only the first kStreamRows rows
+// of the tables in shared memory -- |v|^2 < 10^(-6 + 22 * 3072 / 10000) = 5.7 m^2/s^2, four orders of magnitude above what
+// the BASELINE configurations reach -- and reads higher rows from the global image; the freed shared memory holds its
+// chunk pipeline.  Layout of a window of R rows: thr[R] (8 B each), edge[R or kRows + 1] (4 B each), then the cell bounds.
+constexpr int kStreamRows = 3072;
+__host__ __device__ constexpr int smem_edge_off(int R) { return R == kRows ? kThrBytes : R * 8; }
+__host__ __device__ constexpr int smem_bnd_off(int R) { return R == kRows ? kTableSmemBytes : R * 12; }
+
 struct Soa {
     float *x, *y, *z, *vx, *vy, *vz, *ax, *ay, *az;
     int* ts;
@@ -174,11 +182,14 @@ __device__ __forceinline__ unsigned long long child_id(unsigned long long parent
 // The result equals the reference formula for EVERY fp32 E: the edge table is checked against the double formula on
 // the CPU (tests/tools/check_energy_index.cpp), the estimate-and-probe against a bisection of that table on the
 // device (k_sweep_energy_index, all 2^31 non-negative bit patterns).
-__device__ __forceinline__ int energy_index(float e, const float* __restrict__ s_edge) {
+__device__ __forceinline__ int energy_row_estimate(float e) {       // the row, or the one above it
     float lg;
     asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(e));
     const float s = __fmaf_rn(lg, 136.83181621090054f, 2727.2727272727275f);   // *log10(2)*1e4/22, +6e4/22
-    const int j = max(0, min(__float2int_rn(s), kRows - 1));
+    return max(0, min(__float2int_rn(s), kRows - 1));
+}
+__device__ __forceinline__ int energy_index(float e, const float* __restrict__ s_edge) {
+    const int j = energy_row_estimate(e);
     return j - ((e < s_edge[j]) ? 1 : 0);
 }
 // the same index by bisection of the edge table (no estimate involved): the yardstick of the device-side sweep

@@ -369,10 +369,12 @@ int Sim::create(const picb200_config* c) {
 
     if (const char* pad = getenv("PICB200_SMEM_PAD")) fused_smem_pad = std::max(0, std::min(atoi(pad), 227 * 1024 - 512 - kFusedSmemBytes(1024)));
     CK(cudaFuncSetAttribute(k_mover<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
-    CK(cudaFuncSetAttribute(k_poisson_fused<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024) + fused_smem_pad), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024, true)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_poisson_fused<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFusedSmemBytes(1024, true)), "Mover attr");
     fused = (cfg.mode == PICB200_MODE_DYNAMIC || cfg.mode == PICB200_MODE_DYNAMIC_OLD) && !getenv("PICB200_NO_FUSE");
     if (const char* fr = getenv("PICB200_FIELD_RATIO")) field_ratio = atoi(fr);
     // several ranks: the pass over the union box and its grid barrier are paid per rank whatever the slab holds: large slabs only
@@ -386,10 +388,12 @@ int Sim::create(const picb200_config* c) {
         {
             PeerSync init;
             memset(&init, 0, sizeof(init));
+            for (int p = 0; p < 2; ++p)
+                for (int q = 0; q < kMaxRanks; ++q) init.box[p][q] = 1023ull << 54;      // exchange number 1023: not before 1023 exchanges, by when it has been overwritten
             PeerLocal pl0;
             memset(&pl0, 0, sizeof(pl0));
             for (int p = 0; p < 2; ++p)
-                for (int k = 0; k < 3; ++k) { init.box_lo[p][k] = kGrid; init.box_hi[p][k] = -1; pl0.sbox_lo[p][k] = kGrid; pl0.sbox_hi[p][k] = -1; }
+                for (int k = 0; k < 3; ++k) { pl0.sbox_lo[p][k] = kGrid; pl0.sbox_hi[p][k] = -1; }
             CK(cudaMalloc(&psync, sizeof(PeerSync)), "Minor alloc");
             CK(cudaMemcpy(psync, &init, sizeof(init), cudaMemcpyHostToDevice), "Minor alloc");
             CK(cudaMalloc(&pl, sizeof(PeerLocal)), "Minor alloc");
@@ -478,6 +482,7 @@ int Sim::peer_connect(const void* handles) {
     // connect before the first population is created (the grids are still all-zero then)
     if (charge_valid) return fail("picb200_peer_connect must precede the first Poisson step", "Peer setup");
     pa.debug = getenv("PICB200_PEER_DEBUG") ? atoi(getenv("PICB200_PEER_DEBUG")) : 0;
+    pa.strict = (getenv("PICB200_PEER_FENCE") && !strcmp(getenv("PICB200_PEER_FENCE"), "sys")) ? 1 : 0;
     peer_connected = true;
     return 0;
 }
@@ -704,11 +709,14 @@ int Sim::fused_steps(int steps) {
         }
         void* args[] = {&a};
         span_begin(kPhMover);
+        // which step loop: adopting from kAdoptMinSteps mobility steps per Poisson step, streaming up to kStreamMaxSteps (HBM-side)
         const bool adopt = cfg.poisson_timestep >= (getenv("PICB200_ADOPT_STEPS") ? atoi(getenv("PICB200_ADOPT_STEPS")) : kAdoptMinSteps);
-        const void* kern = peer ? (adopt ? (const void*)k_poisson_fused<true, true> : (const void*)k_poisson_fused<true, false>)
-                                : (adopt ? (const void*)k_poisson_fused<false, true> : (const void*)k_poisson_fused<false, false>);
-        CK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)sm_count),
-                                       dim3((unsigned)mover_threads), args, (size_t)kFusedSmemBytes(mover_threads) + fused_smem_pad, stream),
+        const bool streaming = !adopt && mover_threads == 1024 && cfg.poisson_timestep <= (getenv("PICB200_STREAM_STEPS") ? atoi(getenv("PICB200_STREAM_STEPS")) : kStreamMaxSteps);
+        const int variant = adopt ? 1 : (streaming ? 2 : 0);
+        static const void* const kernels[2][3] = {{(const void*)k_poisson_fused<false, 0>, (const void*)k_poisson_fused<false, 1>, (const void*)k_poisson_fused<false, 2>},
+                                                  {(const void*)k_poisson_fused<true, 0>, (const void*)k_poisson_fused<true, 1>, (const void*)k_poisson_fused<true, 2>}};
+        CK(cudaLaunchCooperativeKernel(kernels[peer ? 1 : 0][variant], dim3((unsigned)sm_count), dim3((unsigned)mover_threads), args,
+                                       streaming ? (size_t)kFusedSmemBytes(mover_threads, true) : (size_t)kFusedSmemBytes(mover_threads) + fused_smem_pad, stream),
            "Mobility steps");
         ++launches; ++mover_launches;
         span_end();

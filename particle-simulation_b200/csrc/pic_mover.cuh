@@ -53,6 +53,8 @@ struct MoverCtx {
     DevState* st;
     const float2* thr;
     const float* edge;
+    const float2* g_thr;   // the whole tables in global memory (rows beyond a shared-memory window of kStreamRows)
+    const float* g_edge;
     uint32_t* stage;
     int stage_cap;       // entries of the stage in use: 32 (k_mover) or kSS (fused kernel)
     int cap, pt, lane, stepwise;
@@ -129,9 +131,22 @@ __device__ __forceinline__ void stage_spill(const MoverCtx& c, int count) {
     __syncwarp();
 }
 
+// {T(split), T(split + remove)} of the table row of energy `en` (energyToIndex, src/cross_section.cu:32-35): estimate, one
+// probe of the exact bin edge, one 8-byte row.  kSmemRows < kRows: shared memory holds the first kSmemRows rows only.
+template <int kSmemRows>
+__device__ __forceinline__ float2 collision_row(const MoverCtx& c, float en) {
+    const int j = energy_row_estimate(en);
+    if (kSmemRows < kRows && j >= kSmemRows) {
+        const int idx = j - ((en < __ldg(c.g_edge + j)) ? 1 : 0);
+        return __ldg(c.g_thr + idx);
+    }
+    const int idx = j - ((en < c.edge[j]) ? 1 : 0);
+    return c.thr[idx];
+}
+
 // Push one lane's electron through mobility steps max(t_begin.., t0) .. t_to; all 32 lanes run the
 // same step together.  Spawned children are ranked into the warp's stage.
-template <bool kCountSpill>
+template <bool kCountSpill, int kSmemRows = kRows>
 __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, int t0, int t_to, int& staged,
                                         unsigned& pushes, int& dead, bool& touched) {
     const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
@@ -166,7 +181,7 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
                 const uint32_t w = (g & 2u) ? w23 : w01;
                 const float r = __uint2float_rn(w);          // the rows hold thresholds on float(w): draw_threshold() on the host
                 const float en = __fmaf_rn(e.vz, e.vz, __fmaf_rn(e.vy, e.vy, __fmul_rn(e.vx, e.vx)));
-                const float2 th = c.thr[energy_index(en, c.edge)];
+                const float2 th = collision_row<kSmemRows>(c, en);
                 if (r < th.x) {              // ionisation: the child copies the pre-flip state
                     spawn = true;
                     cvx = e.vx; cvy = e.vy; cvz = e.vz;
@@ -306,6 +321,8 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     c.st = a.st;
     c.thr = reinterpret_cast<const float2*>(smem_raw);
     c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
+    c.g_thr = reinterpret_cast<const float2*>(a.tables);
+    c.g_edge = reinterpret_cast<const float*>(reinterpret_cast<const unsigned char*>(a.tables) + kThrBytes);
     c.stage = reinterpret_cast<uint32_t*>(smem_raw + kTableSmemBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
     c.cap = a.capacity;
     c.pt = a.pt;
@@ -592,7 +609,8 @@ __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, 
 // the whole warp, because the new occupants have other ids.  `slot_ok`: the lane has a slot to offer.
 constexpr int kAdoptMin = 1;        // measured at cfg5, poisson_timestep = 100: 1 -> 114 ms, 4 -> 122, 8 -> 132, never -> 163
 constexpr int kAdoptMinSteps = 24;   // poisson_timestep from which chunks use the adopting loop
-template <bool kStaged, bool kAdopt>
+constexpr int kStreamMaxSteps = 3;   // poisson_timestep up to which chunks are streamed (k_poisson_fused, kVariant 2)
+template <bool kStaged, bool kAdopt, int kSmemRows = kRows>
 __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float& y, float& z, float& vx, float& vy, float& vz,
                                               float& ax, float& ay, float& az, unsigned long long& id, bool& alive,
                                               int tb, const int t_first, int& staged, unsigned& pushes, int& dead,
@@ -622,7 +640,7 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
         const uint32_t w01 = (g & 1u) ? rnd.y : rnd.x, w23 = (g & 1u) ? rnd.w : rnd.z;
         const float r = __uint2float_rn((g & 2u) ? w23 : w01);   // the rows hold thresholds on float(w): draw_threshold() on the host
         const float en = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, __fmul_rn(vx, vx)));
-        const float2 th = c.thr[energy_index(en, c.edge)];
+        const float2 th = collision_row<kSmemRows>(c, en);
         const bool coll = act & !oob;
         const bool spawn = coll & (r < th.x);                    // ionisation
         const bool die = act & (oob | (!spawn & (r < th.y)));    // left the domain, or attachment
@@ -682,7 +700,7 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
     }
 }
 
-template <bool kLaterGen>
+template <bool kLaterGen, int kSmemRows = kRows>
 __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead) {
     const int i = i0 + c.lane;
     const bool in = i < end;
@@ -707,11 +725,11 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
     if (kLaterGen) {                        // spilled children (ts = birth step): the lockstep loop, each from its own step on
         const int t_first = __reduce_min_sync(kFull, was_alive ? ts : 0x3fffffff) + 1;
         int none = 0;
-        lockstep_push<true, false>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, ts, t_first, staged, pushes, dead, false, none);
+        lockstep_push<true, false, kSmemRows>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, ts, t_first, staged, pushes, dead, false, none);
         touched = true;
     } else {
         const int t0 = max(1, ts + 1);      // src/pic.cu:218
-        advance<true>(c, e, alive, t0, c.pt, staged, pushes, dead, touched);
+        advance<true, kSmemRows>(c, e, alive, t0, c.pt, staged, pushes, dead, touched);
     }
     if (was_alive) {
         if (touched) {
@@ -730,21 +748,52 @@ __device__ __forceinline__ void fused_chunk(const MoverCtx& c, const FusedCtx& f
 // mobility step t, so the step loop is straight-line code: the Philox block changes for the whole
 // warp at once, dead lanes keep computing values nobody stores instead of branching around the body,
 // and the only branch is the warp vote "somebody spawned".
-template <bool kAdopt>
-__device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead, int& npool) {
+// cp.async (LDGSTS) copies of one chunk's arrays into a warp-private buffer: no registers are held while the data is in
+// flight, so the loads of the NEXT chunk overlap the pushes of the current one.
+__device__ __forceinline__ void stream_issue(const MoverCtx& c, int i0, int end, uint32_t* sb) {
+    const int i = i0 + c.lane;
+    if (i < end) {
+        const unsigned d = (unsigned)__cvta_generic_to_shared(sb + c.lane);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(c.s.x + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 128u), "l"(c.s.y + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 256u), "l"(c.s.z + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 384u), "l"(c.s.vx + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 512u), "l"(c.s.vy + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 640u), "l"(c.s.vz + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 768u), "l"(c.s.ts + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(sb + 224) + 8u * (unsigned)c.lane), "l"(c.s.id + i) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void stream_wait_older() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// kStream: the chunk's eight arrays were copied into the warp's shared-memory buffer `sb` by cp.async while the previous
+// chunk was pushed (stream_issue): lane-indexed words x y z vx vy vz ts, then the 64-bit ids.
+constexpr int kStreamWordsPerChunk = 9 * 32;
+template <bool kAdopt, bool kStream>
+__device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead, int& npool,
+                                                 const uint32_t* sb = nullptr) {
+    constexpr int kSmemRows = kStream ? kStreamRows : kRows;
     const int i = i0 + c.lane;
     const bool in = i < end;
     float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f;
     unsigned long long id = 0;
     int ts = -1;
     if (in) {
-        x = __ldcg(c.s.x + i); y = __ldcg(c.s.y + i); z = __ldcg(c.s.z + i);
-        vx = __ldcg(c.s.vx + i); vy = __ldcg(c.s.vy + i); vz = __ldcg(c.s.vz + i);
-        ts = __ldcg(c.s.ts + i);
-        id = __ldcg(c.s.id + i);
+        if (kStream) {
+            x = __uint_as_float(sb[c.lane]); y = __uint_as_float(sb[32 + c.lane]); z = __uint_as_float(sb[64 + c.lane]);
+            vx = __uint_as_float(sb[96 + c.lane]); vy = __uint_as_float(sb[128 + c.lane]); vz = __uint_as_float(sb[160 + c.lane]);
+            ts = (int)sb[192 + c.lane];
+            id = reinterpret_cast<const unsigned long long*>(sb + 224)[c.lane];
+        } else {
+            x = __ldcg(c.s.x + i); y = __ldcg(c.s.y + i); z = __ldcg(c.s.z + i);
+            vx = __ldcg(c.s.vx + i); vy = __ldcg(c.s.vy + i); vz = __ldcg(c.s.vz + i);
+            ts = __ldcg(c.s.ts + i);
+            id = __ldcg(c.s.id + i);
+        }
     }
     if (__any_sync(kFull, (ts != -1) & (ts != kDead))) {      // uploaded populations may carry other timestamps
-        fused_chunk<false>(c, f, i0, end, staged, pushes, dead);
+        fused_chunk<false, kSmemRows>(c, f, i0, end, staged, pushes, dead);
         return;
     }
     const bool was_alive = in & (ts != kDead);                // holes of earlier Poisson steps stay in place (lazy compaction)
@@ -758,7 +807,7 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
     }
     bool alive = was_alive;
     int n_adopted = 0;                                            // children this lane took over from their parents' lanes
-    lockstep_push<false, kAdopt>(c, x, y, z, vx, vy, vz, ax, ay, az, id, alive, 0, 1, staged, pushes, dead, in, n_adopted);
+    lockstep_push<false, kAdopt, kSmemRows>(c, x, y, z, vx, vy, vz, ax, ay, az, id, alive, 0, 1, staged, pushes, dead, in, n_adopted);
     if (kAdopt && __any_sync(kFull, n_adopted > 0)) {
         // adopted children were born like any other: the reference's counter n decides whether they exist
         // (src/pic.cu:222).  One atomic per chunk; the lane's LAST adoption has the highest index, the
@@ -852,6 +901,7 @@ __device__ __forceinline__ void load_stage_entry(const MoverCtx& c, const uint32
 }
 
 // k children in registers (lane < k: electron e, born at step tb): slots, remaining pushes, one store, deposit
+template <int kSmemRows>
 __device__ __forceinline__ void fused_batch(const MoverCtx& c, const FusedCtx& f, El& e, int tb, int k, int& staged, unsigned& pushes, int& dead, int& npool) {
     // the first p children move into free slots this warp holds, the others go above the high-water mark
     const int p = min(k, npool);
@@ -867,7 +917,7 @@ __device__ __forceinline__ void fused_batch(const MoverCtx& c, const FusedCtx& f
     bool alive = born;
     const int t_first = __reduce_min_sync(kFull, born ? tb : 0x3fffffff) + 1;
     int none = 0;
-    lockstep_push<true, false>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, tb, t_first, staged, pushes, dead, false, none);
+    lockstep_push<true, false, kSmemRows>(c, e.x, e.y, e.z, e.vx, e.vy, e.vz, e.ax, e.ay, e.az, e.id, alive, tb, t_first, staged, pushes, dead, false, none);
     if (__any_sync(kFull, born & !in)) {                     // rare: no room above the holes -> parked until this step's compaction
         const bool park = born && !in && alive;
         const unsigned pm = __ballot_sync(kFull, park);
@@ -907,26 +957,40 @@ __device__ __forceinline__ int staged_load(const MoverCtx& c, int& staged, El& e
     __syncwarp();
     return k;
 }
+template <int kSmemRows>
 __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& f, int& staged, unsigned& pushes, int& dead, int& npool) {
     El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     int tb = 0;
     const int k = staged_load(c, staged, e, tb);
-    fused_batch(c, f, e, tb, k, staged, pushes, dead, npool);
+    fused_batch<kSmemRows>(c, f, e, tb, k, staged, pushes, dead, npool);
 }
 
 constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
+__host__ __device__ constexpr int smem_tables_bytes(int R) { return smem_bnd_off(R) + kBndSmemBytes; }      // R == kRows: kAllTableBytes
+constexpr int kStreamBytesPerWarp = 2 * kStreamWordsPerChunk * 4;                        // two chunks in flight per warp
 // per warp: the children stage (whose first bytes double as the peer exchange's row buffer: that runs between
 // barrier 1 and barrier 2, when every stage is empty) and the free-slot pool
 static_assert(kPushStageBytesPerWarp <= kStageBytesPerWarp, "the peer row buffer lives inside the children stage");
-constexpr int kFusedSmemBytes(int threads) { return kAllTableBytes + (threads / 32) * (kStageBytesPerWarp + kPoolSlots * 4); }
+constexpr int kFusedSmemBytes(int threads, bool stream = false) {
+    return smem_tables_bytes(stream ? kStreamRows : kRows) + (threads / 32) * (kStageBytesPerWarp + kPoolSlots * 4 + (stream ? kStreamBytesPerWarp : 0));
+}
 static_assert(kFusedSmemBytes(1024) + 1024 <= 227 * 1024, "shared memory of the fused kernel");
+// both stay inside the 196 KB carve-out (request + static + 1 KB reserved), see "Shared memory against L1" in DESIGN.md
+static_assert(kFusedSmemBytes(1024, true) + 512 + 1024 <= 196 * 1024 && kFusedSmemBytes(1024, false) + 512 + 1024 <= 196 * 1024, "196 KB carve-out");
+static_assert(smem_tables_bytes(kRows) == kAllTableBytes && smem_tables_bytes(kStreamRows) % 16 == 0, "table windows");
 static_assert(kSS >= 32 && kSS <= 64, "stage_select_earliest handles up to 64 entries");
 
 // kAdopt: the chunks use the adopting step loop (lockstep_push); the host picks it for poisson_timestep >= kAdoptMinSteps --
 // it carries more state through every step and only pays when lanes die out long before the Poisson step ends.
-template <bool kPeer, bool kAdopt>
+// kVariant: 0 = plain; 1 = adopt (above); 2 = stream: for small poisson_timestep the step is HBM-side -- a warp then keeps the
+// NEXT chunk's arrays in flight (cp.async into a shared-memory double buffer) while it pushes the current one; the room comes
+// from a shared-memory window of kStreamRows table rows instead of all of them.
+template <bool kPeer, int kVariant>
 __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant__ FusedArgs a) {
+    constexpr bool kAdopt = kVariant == 1, kStream = kVariant == 2;
+    constexpr int kSmemRows = kStream ? kStreamRows : kRows;
+    constexpr int kTablesBytes = smem_tables_bytes(kSmemRows);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ __align__(16) int s_box[8];     // lo xyz, hi xyz of this block's deposits (deposit_lanes reads it as int4 + int2)
     __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
@@ -934,10 +998,17 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     __shared__ int s_dead;
     __shared__ BlockBc bc;
     if (threadIdx.x == 0) { s_ticket = 0; s_pushes = 0; s_dead = 0; }
-    {
+    if (!kStream) {
         const float4* src = reinterpret_cast<const float4*>(a.tables);
         float4* dst = reinterpret_cast<float4*>(smem_raw);
         for (int k = threadIdx.x; k < kAllTableBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
+    } else {        // the first kStreamRows rows of the thresholds and of the edges, then the cell bounds
+        const unsigned char* g = reinterpret_cast<const unsigned char*>(a.tables);
+        for (int k = threadIdx.x; k < kStreamRows * 8 / 16; k += blockDim.x) reinterpret_cast<float4*>(smem_raw)[k] = __ldg(reinterpret_cast<const float4*>(g) + k);
+        for (int k = threadIdx.x; k < kStreamRows * 4 / 16; k += blockDim.x)
+            reinterpret_cast<float4*>(smem_raw + smem_edge_off(kSmemRows))[k] = __ldg(reinterpret_cast<const float4*>(g + kThrBytes) + k);
+        for (int k = threadIdx.x; k < kBndSmemBytes / 16; k += blockDim.x)
+            reinterpret_cast<float4*>(smem_raw + smem_bnd_off(kSmemRows))[k] = __ldg(reinterpret_cast<const float4*>(g + kTableSmemBytes) + k);
     }
     if (threadIdx.x < 6) s_box[threadIdx.x] = threadIdx.x < 3 ? kGrid : -1;
     __syncthreads();
@@ -947,8 +1018,10 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     c.s = a.s;
     c.st = st;
     c.thr = reinterpret_cast<const float2*>(smem_raw);
-    c.edge = reinterpret_cast<const float*>(smem_raw + kThrBytes);
-    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kAllTableBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
+    c.edge = reinterpret_cast<const float*>(smem_raw + smem_edge_off(kSmemRows));
+    c.g_thr = reinterpret_cast<const float2*>(a.tables);
+    c.g_edge = reinterpret_cast<const float*>(reinterpret_cast<const unsigned char*>(a.tables) + kThrBytes);
+    c.stage = reinterpret_cast<uint32_t*>(smem_raw + kTablesBytes) + (threadIdx.x >> 5) * (kStageWords * kSS);
     c.cap = a.capacity;
     c.pt = a.pt;
     c.lane = threadIdx.x & 31;
@@ -958,7 +1031,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     c.seed = a.seed;
     c.keys = &a.keys;
     FusedCtx f;
-    f.bnd = reinterpret_cast<const float*>(smem_raw + kTableSmemBytes);
+    f.bnd = reinterpret_cast<const float*>(smem_raw + smem_bnd_off(kSmemRows));
     f.s_box = s_box;
     f.efc = a.efc;
     f.park = a.park;
@@ -969,7 +1042,9 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     const int gwarp = (int)((threadIdx.x >> 5) * gridDim.x + blockIdx.x), nwarp = (int)(gridDim.x * (blockDim.x >> 5));
     unsigned xe = 0;                                         // kPeer: exchanges completed (same on every rank)
     int* const push_stage = reinterpret_cast<int*>(c.stage);        // peer exchange only, while the stage is empty
-    c.pool = reinterpret_cast<int*>(smem_raw + kAllTableBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPoolSlots;
+    c.pool = reinterpret_cast<int*>(smem_raw + kTablesBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPoolSlots;
+    uint32_t* const sbuf = reinterpret_cast<uint32_t*>(smem_raw + kTablesBytes + (blockDim.x >> 5) * (kStageBytesPerWarp + kPoolSlots * 4)) +
+                           (threadIdx.x >> 5) * (2 * kStreamWordsPerChunk);      // kStream only: this warp's two chunk buffers
     volatile DevState* const v = st;
 
     // ---- what ONE thread per block fetches after each grid barrier (BlockBc): every thread asking L2 for
@@ -1056,11 +1131,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
                 atomicMin(&st->bbox_lo[ls][threadIdx.x], s_box[threadIdx.x]);
                 atomicMax(&st->bbox_hi[ls][threadIdx.x], s_box[3 + threadIdx.x]);
             }
-            grid_barrier(st, seq, [&]() {
-                // the box words of the exchange before this one have been read by everybody long ago (or never written)
-                PeerSync* mysync = a.peer.sync[a.peer.rank];
-                for (int k = 0; k < 3; ++k) { *(volatile int*)&mysync->box_lo[xe & 1u][k] = kGrid; *(volatile int*)&mysync->box_hi[xe & 1u][k] = -1; }
-            }, [&]() { load_box(bc.box_new, v->bbox_lo[ls], v->bbox_hi[ls]); fetch_step_start(xe); });
+            grid_barrier(st, seq, []() {}, [&]() { load_box(bc.box_new, v->bbox_lo[ls], v->bbox_hi[ls]); fetch_step_start(xe); });
+            if (blockIdx.x == 0 && threadIdx.x == 0) peer_send_box(a.peer, e, bc.box_new);
             peer_add_rows(a.peer, p, a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             // the other summed grid still holds the last exchange of the PREVIOUS population: empty it before
             // this block arrives, the peers add the exchange after this one into it
@@ -1068,7 +1140,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             peer_add_drain(c.lane);
             __syncthreads();
             if (threadIdx.x == 0) {
-                peer_arrive(a.peer, e, bc.box_new);
+                peer_arrive(a.peer, e);
                 peer_finish(e);
             }
             __syncthreads();
@@ -1117,15 +1189,39 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
         f.store_acc = last_step;
         // (one copy of each of the two code paths in the instruction stream: the loop runs until the tickets
         // are gone AND the stage is empty)
-        for (bool more = true; more || staged;) {
-            if (more) {
-                int k = 0;
-                if (c.lane == 0) k = smem_fetch_add(&s_ticket, 1);
-                const int chunk = __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
-                more = chunk < chunks;
-                if (more) fused_chunk_fast<kAdopt>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
+        auto take_ticket = [&]() {
+            int k = 0;
+            if (c.lane == 0) k = smem_fetch_add(&s_ticket, 1);
+            return __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
+        };
+        if (!kStream) {
+            for (bool more = true; more || staged;) {
+                if (more) {
+                    const int chunk = take_ticket();
+                    more = chunk < chunks;
+                    if (more) fused_chunk_fast<kAdopt, false>(c, f, chunk << 5, hw0, staged, pushes, dead, npool);
+                }
+                if (staged >= a.drain_at || (!more && staged)) fused_staged<kSmemRows>(c, f, staged, pushes, dead, npool);
             }
-            if (staged >= a.drain_at || (!more && staged)) fused_staged(c, f, staged, pushes, dead, npool);
+        } else {
+            // the same loop with the chunk's loads issued one chunk ahead (one cp.async group per iteration, also when empty)
+            int cur_chunk = take_ticket(), b = 0;
+            bool have = cur_chunk < chunks;
+            if (have) stream_issue(c, cur_chunk << 5, hw0, sbuf);
+            while (have || staged) {
+                bool have_next = false;
+                if (have) {
+                    const int next_chunk = take_ticket();
+                    have_next = next_chunk < chunks;
+                    stream_issue(c, have_next ? next_chunk << 5 : hw0, hw0, sbuf + (b ^ 1) * kStreamWordsPerChunk);
+                    stream_wait_older();
+                    fused_chunk_fast<false, true>(c, f, cur_chunk << 5, hw0, staged, pushes, dead, npool, sbuf + b * kStreamWordsPerChunk);
+                    cur_chunk = next_chunk;
+                    b ^= 1;
+                }
+                have = have_next;
+                if (staged >= a.drain_at || (!have && staged)) fused_staged<kSmemRows>(c, f, staged, pushes, dead, npool);
+            }
         }
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
@@ -1171,14 +1267,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
                     v->cur = nxt;
                 } else {
                     // reset what the NEXT step will collect into: the other local-box slot (everybody read it a step ago)
-                    // and the union-box words of the exchange consumed at the start of this step (the peers write them
-                    // again only after they have seen this rank arrive for exchange xe+1, which comes after this barrier)
-                    PeerSync* mysync = a.peer.sync[a.peer.rank];
                     const int ob = lslot(xe);
-                    for (int k = 0; k < 3; ++k) {
-                        v->bbox_lo[ob][k] = kGrid; v->bbox_hi[ob][k] = -1;
-                        *(volatile int*)&mysync->box_lo[xe & 1u][k] = kGrid; *(volatile int*)&mysync->box_hi[xe & 1u][k] = -1;
-                    }
+                    for (int k = 0; k < 3; ++k) { v->bbox_lo[ob][k] = kGrid; v->bbox_hi[ob][k] = -1; }
                 }
             }, [&]() {
                 fetch_after_b1(nbox);
@@ -1189,8 +1279,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             const int rounded = (hi - lo + 31) & ~31;
             for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31;;) {         // (one call site of fused_staged)
                 const bool have = k < rounded;
-                if (have) { fused_chunk<true>(c, f, lo + k, hi, staged, pushes, dead); k += gridDim.x * blockDim.x; }
-                if (staged >= a.drain_at || (!have && staged)) fused_staged(c, f, staged, pushes, dead, npool);
+                if (have) { fused_chunk<true, kSmemRows>(c, f, lo + k, hi, staged, pushes, dead); k += gridDim.x * blockDim.x; }
+                if (staged >= a.drain_at || (!have && staged)) fused_staged<kSmemRows>(c, f, staged, pushes, dead, npool);
                 if (!have && !staged) break;
             }
             lo = hi;
@@ -1203,6 +1293,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             // every local deposit of this step is in place: hand the rows of this rank's box to the copy engine,
             // which adds them into the summed grid of every rank over NVLink (asynchronous bulk reduce-adds),
             // and empty the grid this step gathered from
+            if (blockIdx.x == 0 && threadIdx.x == 0) peer_send_box(a.peer, xe + 1u, bc.box_new);
             peer_add_rows(a.peer, (int)((xe + 1u) & 1u), a.grid[2], bc.box_new, gwarp, nwarp, c.lane, push_stage);
             PIC_TRACE(11);
             clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
@@ -1215,7 +1306,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
         if (kPeer) {
             peer_add_drain(c.lane);
             __syncthreads();
-            if (threadIdx.x == 0) peer_arrive(a.peer, xe + 1u, bc.box_new);
+            if (threadIdx.x == 0) peer_arrive(a.peer, xe + 1u);
         }
         PIC_TRACE(4);
         if (compact) {

@@ -13,11 +13,19 @@
 // kernel: the whole run stays one cooperative launch per GPU.
 //
 // Synchronisation (round 2): ONE cross-GPU barrier per exchange, counted by remote atomics -- no system-scope
-// grid barrier, no mailbox round trip.  A block that has drained its bulk adds fences at system scope and does
-// one `red.release.sys.add` on the arrival counter of every rank (its own included); a block may go on to the
-// next Poisson step as soon as ITS rank's counter shows that all blocks of all ranks have arrived
-// (`ld.acquire.sys` spin by one thread per block).  The union of the ranks' deposit boxes travels the same way:
-// `red.min` / `red.max` on six words per rank, issued by one block before its arrival.
+// grid barrier, no mailbox round trip, and no system-scope fence: a phase trace with the bulk adds switched off
+// (PICB200_PEER_DEBUG=3) showed that of the 23 us the exchange cost per Poisson step, 11 us were the
+// `fence.sys` in front of the arrival and 8 us the `red.release.sys` + the acquire.sys polling -- not the
+// megabyte on the wire.  A block whose lanes have waited for their bulk adds (`cp.async.bulk.wait_group 0`: the
+// adds have been PERFORMED at the destination's L2, the point of coherence of that memory, and acknowledged)
+// meets at a block barrier; one thread then does a relaxed `red.sys.add` on the arrival counter of every peer and a
+// gpu-scope release-add on its own rank's counter.  The arrival cannot overtake data that has already been
+// performed.  A block may go on to the next Poisson step as soon as ITS rank's counter shows that all blocks of all
+// ranks have arrived (relaxed polling of a word in local memory, one gpu-scope fence after it).  What the peers
+// later add into this rank's memory (exchange e+2 into the rows this block has just zeroed) arrives at this rank's
+// L2 at least one Poisson step after the gpu-scope release.  PICB200_PEER_FENCE=sys restores system-scope fences on
+// both sides.  The ranks' deposit boxes travel as ONE 8-byte word per source rank (box + exchange number: a
+// single-copy-atomic store, so a box is never seen without its number), written by one thread right after barrier 1.
 //
 // Buffers per rank: L = its local deposit (grid 2), S[0], S[1] = summed grids of even / odd exchanges
 // (grids 0, 1; peers add into them).  Exchange e fills S[e&1]; the step after it gathers from S[e&1] and, once
@@ -34,9 +42,8 @@ constexpr int kMaxRanks = 8;
 // Everything in it is written by remote atomics of the peers (and reset by the owner at a time when no peer can
 // be writing, see above).
 struct PeerSync {
-    alignas(128) unsigned arrive[2];       // per exchange parity: arrivals so far = (exchanges of that parity) x ranks x blocks
-    alignas(128) int box_lo[2][3];         // per exchange parity: union of the ranks' deposit boxes (lo > hi: empty)
-    int box_hi[2][3];
+    alignas(128) unsigned arrive[2];                   // per exchange parity: arrivals so far = (exchanges of that parity) x ranks x blocks
+    alignas(128) unsigned long long box[2][kMaxRanks]; // per exchange parity and SOURCE rank: {lo xyz, hi xyz: 9 bits each, exchange number: 10 bits}
 };
 
 // Owned by the rank, survives picb200_upload / init (the exchange counter must never run backwards).
@@ -52,6 +59,7 @@ struct PeerArgs {
     PeerSync* sync[kMaxRanks];      // sync block of rank r as mapped into this GPU's address space (own rank: local pointer)
     int* sum[kMaxRanks][2];         // summed grids S[0], S[1] of rank r, likewise
     PeerLocal* pl;
+    int strict;                     // PICB200_PEER_FENCE=sys: system-scope fences around the arrival (see above)
     int debug;                      // PICB200_PEER_DEBUG (timing experiments only, results are wrong): 1 = skip the add into the own grid, 2 = skip the adds into the peers' grids
 };
 
@@ -68,8 +76,25 @@ __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
 __device__ __forceinline__ void red_release_sys_add(unsigned* p, unsigned v) {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ void red_sys_min(int* p, int v) { asm volatile("red.relaxed.sys.global.min.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
-__device__ __forceinline__ void red_sys_max(int* p, int v) { asm volatile("red.relaxed.sys.global.max.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void red_relaxed_sys_add(unsigned* p, unsigned v) {
+    asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_gpu_add(unsigned* p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned ld_relaxed_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 constexpr int kPushSegCells = 64;                       // cells staged per bulk operation (256 B per warp)
 constexpr int kPushStageBytesPerWarp = kPushSegCells * 4;
@@ -121,19 +146,22 @@ __device__ __forceinline__ void peer_add_drain(int lane) {
     if (lane == 0) bulk_wait_all();
 }
 
+// ONE thread of the rank, right after barrier 1 (the box of the local deposit is final): this rank's box and the exchange
+// number as one word into every rank's sync block, its own included.
+__device__ __forceinline__ void peer_send_box(const PeerArgs& P, unsigned e, const int* box /* lo xyz, hi xyz of the local deposit */) {
+    const bool mine = box[3] >= box[0] && box[4] >= box[1] && box[5] >= box[2];
+    unsigned long long w = mine ? ((unsigned long long)(box[0] | (box[1] << 9) | (box[2] << 18)) | ((unsigned long long)(box[3] | (box[4] << 9) | (box[5] << 18)) << 27))
+                                : 1ull;                                  // lo x = 1, hi x = 0: empty
+    w |= (unsigned long long)(e & 1023u) << 54;
+    for (int k = 1; k <= P.nranks; ++k) st_relaxed_sys_u64(&P.sync[(P.rank + k) % P.nranks]->box[e & 1u][P.rank], w);
+}
 // ONE thread per block, after a __syncthreads() that follows peer_add_drain() and the block's share of the clearing
-// of the old summed grid: this block's contribution to exchange `e` is complete.  Block 0 also contributes the
-// rank's deposit box to the union (before its own arrival, so that whoever sees the arrival sees the box).
-__device__ __forceinline__ void peer_arrive(const PeerArgs& P, unsigned e, const int* box /* lo xyz, hi xyz of the local deposit */) {
+// of the old summed grid: this block's contribution to exchange `e` is complete.
+__device__ __forceinline__ void peer_arrive(const PeerArgs& P, unsigned e) {
     const int p = (int)(e & 1u);
-    __threadfence_system();          // the bulk adds this block has waited for, and its plain stores, before the arrival
-    if (blockIdx.x == 0 && box[3] >= box[0] && box[4] >= box[1] && box[5] >= box[2]) {
-        for (int k = 1; k <= P.nranks; ++k) {
-            PeerSync* s = P.sync[(P.rank + k) % P.nranks];
-            for (int a = 0; a < 3; ++a) { red_sys_min(&s->box_lo[p][a], box[a]); red_sys_max(&s->box_hi[p][a], box[3 + a]); }
-        }
-    }
-    for (int k = 1; k <= P.nranks; ++k) red_release_sys_add(&P.sync[(P.rank + k) % P.nranks]->arrive[p], 1u);
+    if (P.strict) __threadfence_system();
+    for (int k = 1; k < P.nranks; ++k) red_relaxed_sys_add(&P.sync[(P.rank + k) % P.nranks]->arrive[p], 1u);
+    red_release_gpu_add(&P.sync[P.rank]->arrive[p], 1u);        // the block's plain stores (rows of L and of the old grid zeroed) before its own rank goes on
 }
 // Arrivals this rank's counter of parity e&1 shows once exchange e is complete everywhere: exchanges 1..e of that
 // parity, each with one arrival per block of every rank (the ranks run equal grids).
@@ -142,21 +170,30 @@ __device__ __forceinline__ unsigned peer_arrival_target(const PeerArgs& P, unsig
     return rounds * (unsigned)P.nranks * gridDim.x;
 }
 // ONE thread per block: wait until every block of every rank has arrived for exchange `e`, i.e. until all rows have
-// been added into this rank's S[e&1]; returns the union box.
+// been added into this rank's S[e&1]; returns the union of the ranks' boxes.
 __device__ __forceinline__ void peer_wait_all(const PeerArgs& P, unsigned e, int* box /* out: lo xyz, hi xyz */) {
     const int p = (int)(e & 1u);
     const PeerSync* s = P.sync[P.rank];
     const unsigned target = peer_arrival_target(P, e);
-    if ((int)(ld_acquire_sys_u32(&s->arrive[p]) - target) < 0) {
-        const unsigned long long t0 = timer_ns(), limit = g_barrier_timeout_ns;
-        unsigned spins = 0;
-        while ((int)(ld_acquire_sys_u32(&s->arrive[p]) - target) < 0) {
-            __nanosleep(20);
-            if ((++spins & 255u) == 0u && timer_ns() - t0 > limit) barrier_timeout_abort(3, e);
+    unsigned long long t0 = 0;
+    unsigned spins = 0;
+    while ((int)(ld_relaxed_sys_u32(&s->arrive[p]) - target) < 0) {
+        if (spins == 0) t0 = timer_ns();
+        __nanosleep(20);
+        if ((++spins & 255u) == 0u && timer_ns() - t0 > g_barrier_timeout_ns) barrier_timeout_abort(3, e);
+    }
+    for (int a = 0; a < 3; ++a) { box[a] = kGrid; box[3 + a] = -1; }
+    for (int q = 0; q < P.nranks; ++q) {
+        unsigned long long w = ld_relaxed_sys_u64(&s->box[p][q]);
+        while ((unsigned)(w >> 54) != (e & 1023u)) {                 // (sent microseconds before that rank's first arrival: normally there)
+            if (spins == 0) t0 = timer_ns();
+            if ((++spins & 255u) == 0u && timer_ns() - t0 > g_barrier_timeout_ns) barrier_timeout_abort(3, e);
+            w = ld_relaxed_sys_u64(&s->box[p][q]);
+        }
+        const int lo = (int)(w & 0x7ffffffull), hi = (int)((w >> 27) & 0x7ffffffull);
+        if ((lo & 511) <= (hi & 511)) {
+            for (int a = 0; a < 3; ++a) { box[a] = min(box[a], (lo >> (9 * a)) & 511); box[3 + a] = max(box[3 + a], (hi >> (9 * a)) & 511); }
         }
     }
-    for (int a = 0; a < 3; ++a) {
-        box[a] = *(const volatile int*)&s->box_lo[p][a];
-        box[3 + a] = *(const volatile int*)&s->box_hi[p][a];
-    }
+    if (P.strict) __threadfence_system(); else __threadfence();     // acquire: what follows reads the summed grid
 }

@@ -415,6 +415,38 @@ def test_per_cell_field_path_matches_oracle(engine, oracle, ratio, pt):
     assert_state_equal(d, o.download_sorted())
 
 
+@pytest.mark.parametrize("stream_steps,pt", [(0, 1), (3, 1), (3, 2), (3, 3), (16, 10)])
+def test_streaming_step_loop_matches_oracle(engine, oracle, monkeypatch, stream_steps, pt):
+    """Small poisson_timestep: the fused kernel streams its chunks (cp.async double buffer, a shared-memory window of the
+    first 3072 table rows; k_poisson_fused kVariant 2).  PICB200_STREAM_STEPS moves the threshold (0: never; 16: also at
+    poisson_timestep 10).  A third of the electrons is fast enough (|v|^2 > 5.7) to use table rows BEYOND the window,
+    which come from the global image.  Same bits as the oracle; ragged population (not a multiple of 32)."""
+    rows = np.zeros((10000, 2), dtype=np.float32)
+    rows[:, 0] = 1.5 + (np.arange(10000) % 7) * 0.25          # every row different from its neighbours: a wrong row shows
+    rows[:, 1] = 1.0 + (np.arange(10000) % 5) * 0.2
+    rng = np.random.default_rng(5)
+    n = 100003
+    pos = rng.uniform(2.45, 2.75, size=(3, n)).astype(np.float32)
+    vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)
+    vel[:, ::3] *= 60.0                                       # |v| ~ 3-5 m/s: rows ~3100-3400
+    monkeypatch.setenv("PICB200_STREAM_STEPS", str(stream_steps))
+    steps = 12 if pt < 10 else 4
+    with engine.Sim(capacity=6 * n, poisson_timestep=pt, mode=0, table_rows=rows, poisson_steps=steps) as sim:
+        sim.upload(*pos, *vel)
+        sim.run_steps(steps // 2)
+        sim.run_steps(steps - steps // 2)
+        m, d = sim.summary(), sim.download()
+    o = oracle.Oracle(capacity=6 * n, poisson_timestep=pt, table_rows=rows, threads=4)
+    o.upload(*pos, *vel)
+    o.run(steps)
+    c = o.counters()
+    assert (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"])
+    assert c["added"] > 1000 and c["removed"] > 1000
+    assert_state_equal(d, o.download_sorted())
+    e = np.stack([d.vx, d.vy, d.vz]).astype(np.float64)
+    assert ((e ** 2).sum(axis=0) > 5.7).sum() > 1000           # rows beyond the window were in use until the end
+
+
 def test_lazy_compaction_parks_children_near_capacity(engine, oracle):
     """Holes in place shift the slots of new children upwards; a child whose shifted slot passes the capacity
     while the reference's counter does not is parked and placed by the compaction the step then ends with.

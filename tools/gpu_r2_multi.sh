@@ -23,3 +23,8 @@ d=json.loads(open("$O/bench_n1.json").read().strip().splitlines()[-1]); print("N
 PY
 for a in "30 0 10000000 10 256 100000000 100 1" "30 0 10000000 10 256 100000000 100 10" "30 0 10000000 10 256 100000000 100 100"; do
   echo "$a :: $(PICB200_PRINT_PUSHES=1 ./run $a 2>&1 | grep -E 'GPU time|pushes' | tr '\n' ' ')"; done
+if [ "${FENCE_AB:-0}" = "1" ]; then
+PICB200_PEER_FENCE=sys PICB200_BENCH_NO_CFG4=1 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 bench.py --gpus $N --steps 5 --warmup 3 2> $O/bench_sys_n$N.err | python -c "
+import json,sys
+d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('PICB200_PEER_FENCE=sys: N=%d value %.4g ms/step %.3f' % (d['n_gpus'], d['value'], d['ms_per_step']), d['parity_check']['ok'])"
+fi

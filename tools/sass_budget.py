@@ -102,7 +102,7 @@ def loops(items):
 
 
 def main():
-    flt = next((a for a in sys.argv[1:] if not a.startswith("--")), "k_poisson_fusedILb0ELb0")
+    flt = next((a for a in sys.argv[1:] if not a.startswith("--")), "k_poisson_fusedILb0ELi0")
     sec, (loop_line, end_line) = source_sections()
     funcs = disassemble(flt)
     for name, lines in funcs.items():
