@@ -38,8 +38,10 @@ def source_sections():
     sec["leapfrog"] = [(MOVER, find(mv, "const bool act = kStaged", loop), find(mv, "if (!kStaged || act)", loop))]
     sec["bounds"] = [(MOVER, find(mv, "const bool oob =", loop), find(mv, "const bool oob =", loop))]
     sec["draw"] = [(MOVER, find(mv, "const uint32_t w01 =", loop), find(mv, "const float r = __uint2float_rn", loop))]
-    e0 = find(dv, "int energy_index(float e")
-    sec["energy + table row"] = [(MOVER, find(mv, "const float en =", loop), find(mv, "const float2 th =", loop)), (DEVICE, e0, find(dv, "return j - ((e < s_edge[j])", e0))]
+    e0 = find(dv, "int energy_row_estimate(float e")
+    r0 = find(mv, "float2 collision_row(const MoverCtx& c, float en)")
+    sec["energy + table row"] = [(MOVER, find(mv, "const float en =", loop), find(mv, "const float2 th =", loop)), (DEVICE, e0, find(dv, "return j - ((e < s_edge[j])", e0)),
+                                 (MOVER, r0, find(mv, "return c.thr[idx];", r0))]
     sec["collide / die / vote"] = [(MOVER, find(mv, "const bool coll =", loop), find(mv, "unsigned m = __ballot_sync(kFull, spawn);", loop) + 1)]
     sec["loop control"] = [(MOVER, loop - 1, loop + 1)]
     end = find(mv, "if (kAdopt) {\n".strip(), find(mv, "const uint32_t flip =", loop))
