@@ -20,6 +20,7 @@ constexpr int kDead = -2;               // src/electron.h:8
 constexpr int kGrids = 3;               // charge grids in rotation (gather / next deposit / being emptied)
 constexpr int kRot = 3;
 constexpr int kBoxes = kGrids + 1;      // bounding-box slots in DevState
+constexpr int kMaxBlocks = 160;         // blocks of the persistent kernel the quota balancer handles (5 per lane of one warp)
 constexpr unsigned kFull = 0xffffffffu;
 constexpr uint32_t kTagCollide = 0u, kTagInit = 1u;
 
@@ -78,6 +79,9 @@ struct DevState {
     alignas(128) unsigned bar_release;          // grid barrier: releases
     alignas(128) int n_parked;                  // parking cursor
     alignas(128) int pad_;
+    // fused kernel, load balance: chunks per microsecond each block managed in its main phase (running mean), one set per
+    // Poisson-step parity -- a block publishes into the set the NEXT step reads (k_poisson_fused, "quotas")
+    float rate[2][kMaxBlocks];
 };
 
 struct StepLog { int n_after_mobility, n_after_compaction; };

@@ -424,6 +424,7 @@ struct FusedArgs {
     int field_min_n;             // ... and the rank holds at least this many electrons (peer mode: the pass costs a barrier per rank)
     int test_desert;             // PICB200_TEST_DESERT=1 (tests): the last block leaves the kernel at once -> the grid barrier must time out
     PhiloxKeys keys;             // philox_round_keys(seed)
+    int balance;                 // chunks are dealt to the blocks in proportion to their measured speed (PICB200_BALANCE=0: equal shares)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -983,6 +984,70 @@ static_assert(kSS >= 32 && kSS <= 64, "stage_select_earliest handles up to 64 en
 
 // kAdopt: the chunks use the adopting step loop (lockstep_push); the host picks it for poisson_timestep >= kAdoptMinSteps --
 // it carries more state through every step and only pays when lanes die out long before the Poisson step ends.
+// Quotas.  Chunks are dealt to the blocks round-robin (chunk k of block b is global chunk k * gridDim + b: the same SM
+// sees the same lines every step, which keeps them on its side of the L2), and with equal shares a Poisson step ends
+// with its SLOWEST block: on the HBM-side corner the blocks' main phases took 178 / 192 / 206 / 220 us, the same blocks
+// every step (correlation 0.99 from step to step: SMs of the larger GPCs share the GPC's port to the L2 with more
+// neighbours) -- 13 % of the step spent waiting at the barrier.  So the shares follow the measured speed: every block
+// publishes the chunks per microsecond it managed (a running mean); at the start of a step warp 0 of every block
+// turns the SAME 148 numbers into the same cumulative shares.  All blocks still take the first `base` = min share
+// rounds round-robin; what a block gets beyond that is a contiguous range after those rounds.  Results do not depend
+// on who pushes which chunk.  q[0] = base, q[1] = first chunk of this block's extra range, q[2] = its length.
+__device__ __forceinline__ void block_quota(const float* __restrict__ rate, int chunks, int lane, int* q) {
+    const int G = (int)gridDim.x;
+    float r[5];
+    bool ok = true;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int b = lane * 5 + j;
+        r[j] = b < G ? __ldcg(rate + b) : 0.f;
+        ok = ok && (b >= G || r[j] > 0.f);
+    }
+    if (!__all_sync(kFull, ok)) {                            // no history yet (first step after an upload): equal shares
+        if (lane == 0) { q[0] = 0x7fffffff; q[1] = 0; q[2] = 0; }
+        return;
+    }
+    float sum = r[0] + r[1] + r[2] + r[3] + r[4];
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(kFull, sum, o);
+    const float mean = sum / (float)G, lo = 0.67f * mean, hi = 1.5f * mean;      // one odd measurement must not starve a block
+    float pre[5], acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int b = lane * 5 + j;
+        acc += b < G ? fminf(fmaxf(r[j], lo), hi) : 0.f;
+        pre[j] = acc;
+    }
+    float off = acc;                                         // inclusive scan of the lanes' totals
+    for (int o = 1; o < 32; o <<= 1) { const float t = __shfl_up_sync(kFull, off, o); if (lane >= o) off += t; }
+    const float total = __shfl_sync(kFull, off, 31);
+    off -= acc;                                              // exclusive
+    int cum[5], share[5];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int b = lane * 5 + j;
+        cum[j] = b >= G - 1 ? chunks : min(chunks, __float2int_rn((float)chunks * ((off + pre[j]) / total)));
+    }
+    int prev = __shfl_up_sync(kFull, cum[4], 1);
+    if (lane == 0) prev = 0;
+    int smin = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int b = lane * 5 + j;
+        share[j] = max(0, cum[j] - (j ? cum[j - 1] : prev));
+        if (j == 0 && cum[0] < prev) cum[0] = prev;          // (rounding can never run backwards: the prefix is monotone)
+        if (b < G) smin = min(smin, share[j]);
+    }
+    smin = __reduce_min_sync(kFull, smin);
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int b = lane * 5 + j;
+        if (b == (int)blockIdx.x) {
+            const int before = j ? cum[j - 1] : prev;        // chunks of the blocks before this one
+            q[0] = smin; q[1] = smin * G + (before - smin * b); q[2] = share[j] - smin;
+        }
+    }
+}
+
 // kVariant: 0 = plain; 1 = adopt (above); 2 = stream: for small poisson_timestep the step is HBM-side -- a warp then keeps the
 // NEXT chunk's arrays in flight (cp.async into a shared-memory double buffer) while it pushes the current one; the room comes
 // from a shared-memory window of kStreamRows table rows instead of all of them.
@@ -994,10 +1059,12 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ __align__(16) int s_box[8];     // lo xyz, hi xyz of this block's deposits (deposit_lanes reads it as int4 + int2)
     __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
+    __shared__ int s_quota[4];     // block_quota(): base, first extra chunk, extra chunks; [3] = Poisson step it is valid for, plus one
+    __shared__ unsigned long long s_t0;   // start of this block's main phase
     __shared__ unsigned long long s_pushes;
     __shared__ int s_dead;
     __shared__ BlockBc bc;
-    if (threadIdx.x == 0) { s_ticket = 0; s_pushes = 0; s_dead = 0; }
+    if (threadIdx.x == 0) { s_ticket = 0; s_pushes = 0; s_dead = 0; s_quota[3] = 0; }
     if (!kStream) {
         const float4* src = reinterpret_cast<const float4*>(a.tables);
         float4* dst = reinterpret_cast<float4*>(smem_raw);
@@ -1189,10 +1256,29 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
         f.store_acc = last_step;
         // (one copy of each of the two code paths in the instruction stream: the loop runs until the tickets
         // are gone AND the stage is empty)
+        // shares by measured speed (block_quota), once the step is long enough for shares to mean anything; until warp 0
+        // has worked them out the warps take the rounds every block takes under any quota (shares are clamped to >= 0.44
+        // of an equal one)
+        const int G = (int)gridDim.x;
+        const bool balanced = a.balance != 0 && G <= kMaxBlocks && chunks >= 16 * G;
+        const int k_free = balanced ? (chunks / G) * 2 / 5 : 0x7fffffff;
+        const int step_tag = step + 1;
+        if (threadIdx.x == 0) s_t0 = globaltimer_ns();
+        if (balanced && threadIdx.x < 32) {
+            block_quota(st->rate[bc.pidx & 1], chunks, c.lane, s_quota);
+            __syncwarp();
+            if (c.lane == 0) { __threadfence_block(); *(volatile int*)&s_quota[3] = step_tag; }
+        }
         auto take_ticket = [&]() {
             int k = 0;
             if (c.lane == 0) k = smem_fetch_add(&s_ticket, 1);
-            return __shfl_sync(kFull, k, 0) * (int)gridDim.x + (int)blockIdx.x;
+            k = __shfl_sync(kFull, k, 0);
+            if (k < k_free) return k * G + (int)blockIdx.x;
+            while (*(volatile int*)&s_quota[3] != step_tag) __nanosleep(20);      // (ready long before anybody gets here)
+            const int base = *(volatile int*)&s_quota[0];
+            if (k < base) { const int chunk = k * G + (int)blockIdx.x; return chunk; }
+            const int j = k - base;
+            return j < *(volatile int*)&s_quota[2] ? *(volatile int*)&s_quota[1] + j : 0x7fffffff;
         };
         if (!kStream) {
             for (bool more = true; more || staged;) {
@@ -1244,6 +1330,15 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             pushes = 0; dead = 0;
             __syncthreads();
             PIC_TRACE(2);      // every warp of the block finished
+            if (a.balance && threadIdx.x == 0 && lo == hw0 && G <= kMaxBlocks) {
+                // chunks per microsecond of this block's main phase, as a running mean, for the next step's shares
+                const int mine = (balanced && s_quota[0] != 0x7fffffff) ? s_quota[0] + s_quota[2] : (chunks - (int)blockIdx.x + G - 1) / G;
+                const float us = (float)(globaltimer_ns() - s_t0) * 1e-3f;
+                const float old = __ldcg(&st->rate[bc.pidx & 1][blockIdx.x]);
+                float now = old;
+                if (mine >= 8 && us > 0.f) { const float meas = (float)mine / us; now = old > 0.f ? 0.5f * old + 0.5f * meas : meas; }
+                __stcg(&st->rate[(bc.pidx & 1) ^ 1][blockIdx.x], now);
+            }
             if (threadIdx.x == 32) {
                 if (s_pushes) atomicAdd(&st->pushes, s_pushes);
                 if (s_dead) atomicAdd(&st->n_dead, s_dead);
