@@ -501,22 +501,25 @@ __device__ __forceinline__ void deposit_lanes(int* __restrict__ grid, bool activ
 }
 
 // Grid-wide barrier; the last block to arrive runs `action` (one thread) before everyone is released.
+// tr (PICB200_TRACE, barrier 1 only): globaltimer stamps [12] arrived, [13] action done (last block only), [14] released
 template <class F, class G>
-__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action, G fetch, bool sys_scope = false) {
+__device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action, G fetch, unsigned long long* tr = nullptr) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        if (sys_scope) __threadfence_system();      // this block's stores into the peers' memory, too
-        else __threadfence();
+        __threadfence();
         const unsigned target = (seq + 1u) * gridDim.x;
         const unsigned prev = atomicAdd(&st->bar_count, 1u);
+        if (tr) tr[12] = timer_ns();
         if (prev + 1u == target) {
             __threadfence();
             action();
+            if (tr) tr[13] = timer_ns();
             __threadfence();
             atomicExch(&st->bar_release, seq + 1u);
         } else {
             barrier_spin(&st->bar_release, seq + 1u, 2, seq);
         }
+        if (tr) tr[14] = timer_ns();
         __threadfence();
         fetch();        // ONE thread per block reads what the next phase needs and leaves it in shared memory
     }
@@ -1061,6 +1064,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     __shared__ int s_ticket;       // next chunk of this block (chunks are dealt to blocks round-robin)
     __shared__ int s_quota[4];     // block_quota(): base, first extra chunk, extra chunks; [3] = Poisson step it is valid for, plus one
     __shared__ unsigned long long s_t0;   // start of this block's main phase
+    __shared__ float s_rate;              // this block's chunks per microsecond (running mean, see the end of the main phase)
     __shared__ unsigned long long s_pushes;
     __shared__ int s_dead;
     __shared__ BlockBc bc;
@@ -1178,7 +1182,10 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
         bc.peer_box_valid = 1;
         fetch_step_start(e);
     };
-    if (threadIdx.x == 0) bc.peer_box_valid = 0;
+    if (threadIdx.x == 0) {
+        bc.peer_box_valid = 0;
+        s_rate = ((int)gridDim.x <= kMaxBlocks) ? __ldcg(&st->rate[ld_volatile_i32(&st->poisson_index) & 1][blockIdx.x]) : 0.f;
+    }
     if (kPeer) {
         xe = ld_sys_u32(&a.peer.pl->xseq);
         if (a.initial_deposit) {
@@ -1331,13 +1338,16 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             __syncthreads();
             PIC_TRACE(2);      // every warp of the block finished
             if (a.balance && threadIdx.x == 0 && lo == hw0 && G <= kMaxBlocks) {
-                // chunks per microsecond of this block's main phase, as a running mean, for the next step's shares
+                // chunks per microsecond of this block's main phase for the next step's shares: the plain mean over the first
+                // eight Poisson steps of a population, then a running mean with weight 1/8 (one step's measurement carries
+                // ~3 % of noise -- children, neighbours -- against a systematic spread of 2 % at cfg2 and 20 % HBM-side)
                 const int mine = (balanced && s_quota[0] != 0x7fffffff) ? s_quota[0] + s_quota[2] : (chunks - (int)blockIdx.x + G - 1) / G;
                 const float us = (float)(globaltimer_ns() - s_t0) * 1e-3f;
-                const float old = __ldcg(&st->rate[bc.pidx & 1][blockIdx.x]);
-                float now = old;
-                if (mine >= 8 && us > 0.f) { const float meas = (float)mine / us; now = old > 0.f ? 0.5f * old + 0.5f * meas : meas; }
-                __stcg(&st->rate[(bc.pidx & 1) ^ 1][blockIdx.x], now);
+                if (mine >= 8 && us > 0.f) {
+                    const float meas = (float)mine / us, w = s_rate > 0.f ? fmaxf(0.125f, 1.0f / (float)(min(bc.pidx, 1 << 20) + 1)) : 1.0f;
+                    s_rate += w * (meas - s_rate);
+                }
+                __stcg(&st->rate[(bc.pidx & 1) ^ 1][blockIdx.x], s_rate);
             }
             if (threadIdx.x == 32) {
                 if (s_pushes) atomicAdd(&st->pushes, s_pushes);
@@ -1368,7 +1378,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             }, [&]() {
                 fetch_after_b1(nbox);
                 if (!kPeer && bc.gen_hi < 0 && !bc.do_compact) fetch_step_start(0u);     // straight on to the next Poisson step
-            });
+            }, a.trace ? a.trace + ((size_t)step * gridDim.x + blockIdx.x) * 16 : nullptr);
             const int hi = bc.gen_hi;
             if (hi < 0) break;
             const int rounded = (hi - lo + 31) & ~31;

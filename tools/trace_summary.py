@@ -14,6 +14,15 @@ comp = t[:, 0, 6] > 0          # steps that ended with a compaction (the others 
 print(f"{t.shape[0]} steps x {blocks} blocks; step time (first start -> last end), us: median {np.median(dur):.1f} mean {dur.mean():.1f}"
       f"; {int(comp.sum())} steps with compaction (mean {dur[comp].mean() if comp.any() else 0:.1f}), {int((~comp).sum())} without (mean {dur[~comp].mean() if (~comp).any() else 0:.1f})")
 tl = t[~comp]
+if tl.shape[0] and tl[:, :, 12].min() > 0:
+    # inside barrier 1: the last block to arrive (the one that stamped slot 13) and everybody's release
+    last = tl[:, :, 13].argmax(1)
+    ar = np.array([tl[s, last[s], 12] for s in range(tl.shape[0])])
+    act = np.array([tl[s, last[s], 13] for s in range(tl.shape[0])])
+    pre = np.array([tl[s, last[s], 12] - tl[s, last[s], 2] for s in range(tl.shape[0])])
+    rel = tl[:, :, 14].max(1)
+    fin = tl[:, :, 3].max(1)
+    print(f"  [barrier 1, last block] syncthreads+fence+arrive {np.median(pre)/1e3:.2f} us, action {np.median(act-ar)/1e3:.2f} us, fence+release seen by all {np.median(rel-act)/1e3:.2f} us, fence+fetch+syncthreads {np.median(fin-rel)/1e3:.2f} us")
 if tl.shape[0]:
     rows = [("own chunks of warp 0 (0->1)", 0, 1), ("wait for block's other warps (1->2)", 1, 2), ("barrier 1 + bookkeeping (2->3)", 2, 3)]
     if tl[:, :, 5].min() > 0:      # peer mode: the exchange follows barrier 1 in every step
