@@ -698,7 +698,7 @@ int Sim::fused_steps(int steps) {
         FusedArgs a{soa, st, tables, {grid[0], grid[1], grid[2]}, holes, movers, log, log_len, cfg.capacity, cfg.poisson_timestep,
                     per_launch, cfg.nranks == 1 ? 1 : 0, efc, seed, nullptr, pa, (peer && !charge_valid) ? 1 : 0, park, park_cap, getenv("PICB200_ADOPT_MIN") ? atoi(getenv("PICB200_ADOPT_MIN")) : kAdoptMin, compact_policy,
                     std::max(1, std::min(kSS, getenv("PICB200_DRAIN_AT") ? atoi(getenv("PICB200_DRAIN_AT")) : kFusedDrainAt)),
-                    (peer || cfg.nranks == 1) ? field : nullptr, field_ratio, field_min_n, getenv("PICB200_TEST_DESERT") ? 1 : 0, philox_round_keys(seed),
+                    (peer || cfg.nranks == 1) ? field : nullptr, field_ratio, field_min_n, getenv("PICB200_TEST_DESERT") ? 1 : 0, philox_round_keys(seed), (getenv("PICB200_WARP_FENCE") && atoi(getenv("PICB200_WARP_FENCE")) == 0) ? 0 : 1,
                     (getenv("PICB200_BALANCE") && atoi(getenv("PICB200_BALANCE")) == 0) ? 0 : 1};
         charge_valid = true;
         // PICB200_TRACE=<file>: dump 16 globaltimer stamps per block per Poisson step of this launch (debugging aid)

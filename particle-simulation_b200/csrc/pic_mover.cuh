@@ -424,6 +424,7 @@ struct FusedArgs {
     int field_min_n;             // ... and the rank holds at least this many electrons (peer mode: the pass costs a barrier per rank)
     int test_desert;             // PICB200_TEST_DESERT=1 (tests): the last block leaves the kernel at once -> the grid barrier must time out
     PhiloxKeys keys;             // philox_round_keys(seed)
+    int warp_fence;              // PICB200_WARP_FENCE=0 switches the per-warp fence at the end of the main phase off (A/B)
     int balance;                 // chunks are dealt to the blocks in proportion to their measured speed (PICB200_BALANCE=0: equal shares)
 };
 
@@ -506,7 +507,9 @@ template <class F, class G>
 __device__ __forceinline__ void grid_barrier(DevState* st, unsigned& seq, F action, G fetch, unsigned long long* tr = nullptr) {
     __syncthreads();
     if (threadIdx.x == 0) {
+        if (tr) tr[15] = timer_ns();
         __threadfence();
+        if (tr) tr[10] = timer_ns();
         const unsigned target = (seq + 1u) * gridDim.x;
         const unsigned prev = atomicAdd(&st->bar_count, 1u);
         if (tr) tr[12] = timer_ns();
@@ -1319,6 +1322,10 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
         // resetGrid, off the critical path: a warp that has run out of chunks empties its rows of the
         // grid that was gathered from in the PREVIOUS Poisson step (nobody touches it during this one)
         if (!kPeer) clear_box_rows(g_old, bc.box_old, gwarp, nwarp, c.lane);
+        // every warp waits for its own stores and deposits to be performed as soon as it is through, while the others are
+        // still pushing: the fence in front of the barrier's arrival then has nothing left to wait for (it was 9 us of
+        // the last block's -- everybody's -- critical path at cfg2)
+        if (a.warp_fence) __threadfence();
         PIC_TRACE(1);          // warp 0 of the block finished its own chunks
 
         // ---- barrier 1 (+ fall-back passes over spilled children).  The last block to arrive at the LAST

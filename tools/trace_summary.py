@@ -20,6 +20,9 @@ if tl.shape[0] and tl[:, :, 12].min() > 0:
     ar = np.array([tl[s, last[s], 12] for s in range(tl.shape[0])])
     act = np.array([tl[s, last[s], 13] for s in range(tl.shape[0])])
     pre = np.array([tl[s, last[s], 12] - tl[s, last[s], 2] for s in range(tl.shape[0])])
+    if tl[:, :, 15].min() > 0:
+        a_ = np.array([[tl[s, last[s], 15] - tl[s, last[s], 2], tl[s, last[s], 10] - tl[s, last[s], 15], tl[s, last[s], 12] - tl[s, last[s], 10]] for s in range(tl.shape[0])])
+        print(f"  [barrier 1, last block] counters + box + block barrier {np.median(a_[:,0])/1e3:.2f} us, fence {np.median(a_[:,1])/1e3:.2f} us, arrival atomic {np.median(a_[:,2])/1e3:.2f} us")
     rel = tl[:, :, 14].max(1)
     fin = tl[:, :, 3].max(1)
     print(f"  [barrier 1, last block] syncthreads+fence+arrive {np.median(pre)/1e3:.2f} us, action {np.median(act-ar)/1e3:.2f} us, fence+release seen by all {np.median(rel-act)/1e3:.2f} us, fence+fetch+syncthreads {np.median(fin-rel)/1e3:.2f} us")
