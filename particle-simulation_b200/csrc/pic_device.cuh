@@ -109,7 +109,7 @@ __device__ int* g_abort_flag = nullptr;
 __device__ unsigned long long g_barrier_timeout_ns = 30ull * 1000ull * 1000ull * 1000ull;
 __device__ __forceinline__ unsigned long long timer_ns() {
     unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");
     return t;
 }
 __device__ __noinline__ void barrier_timeout_abort(int code, unsigned seq) {

@@ -430,7 +430,7 @@ struct FusedArgs {
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");      // ("memory": a stamp must not drift across a block barrier)
     return t;
 }
 #define PIC_TRACE(slot)                                                                             \
