@@ -158,6 +158,15 @@ int picb200_op_mobility(picb200_sim* sim);
 int picb200_op_compact(picb200_sim* sim);
 /* dense copy of charge counts in the inclusive cell box [lo,hi], x fastest */
 int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3], int32_t* out);
+/* picb200_charge_box for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same arguments and result as picb200_charge_box; the packing kernel's scratch is a fixed device array of
+ * PICB200_NOALLOC_MAX_CELLS cells (4 MiB, held by every GPU that loads the library until exit) instead of a cudaMalloc
+ * per call: the call allocates and frees nothing.  A box with more cells is rejected with a clear error (use
+ * picb200_charge_box).  All calls on one GPU share the scratch, which keeps the last call's contents (every cell of the
+ * requested box is overwritten before it is read, nothing needs to start at zero): calls that overlap on the GPU race. */
+#define PICB200_NOALLOC_MAX_CELLS (1 << 20)
+int picb200_charge_box_noalloc(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3], int32_t* out);
 /* cell bounding box of the last deposit (lo > hi when empty) */
 int picb200_charge_bbox(picb200_sim* sim, int32_t lo[3], int32_t hi[3]);
 

@@ -28,6 +28,7 @@ TABLE_ROWS = 10000
 GRID = 512
 ABI_VERSION = 1
 PEER_HANDLE_BYTES = 256
+NOALLOC_MAX_CELLS = 1 << 20
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -107,6 +108,7 @@ SIGNATURES = {
     "picb200_op_mobility": (C.c_int, [_sim]),
     "picb200_op_compact": (C.c_int, [_sim]),
     "picb200_charge_box": (C.c_int, [_sim, _ip, _ip, _ip]),
+    "picb200_charge_box_noalloc": (C.c_int, [_sim, _ip, _ip, _ip]),
     "picb200_charge_bbox": (C.c_int, [_sim, _ip, _ip]),
     "picb200_dev_philox": (C.c_int, [C.c_int32, C.c_int64, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "picb200_dev_energy_index": (C.c_int, [C.c_int32, C.c_int64, _fp, _ip]),
@@ -346,6 +348,15 @@ class Sim:
         shape = tuple(int(v) for v in (hi - lo + 1)[::-1])
         out = np.empty(shape, dtype=np.int32)
         _check(lib.picb200_charge_box(self._h, _ptr(lo, _ip), _ptr(hi, _ip), _ptr(out, _ip)))
+        return out  # indexed [z, y, x]
+
+    def charge_box_noalloc(self, lo, hi):
+        """charge_box() through the entry point that allocates nothing (fixed device scratch of NOALLOC_MAX_CELLS cells)."""
+        lo = np.ascontiguousarray(lo, dtype=np.int32)
+        hi = np.ascontiguousarray(hi, dtype=np.int32)
+        shape = tuple(int(v) for v in (hi - lo + 1)[::-1])
+        out = np.empty(shape, dtype=np.int32)
+        _check(lib.picb200_charge_box_noalloc(self._h, _ptr(lo, _ip), _ptr(hi, _ip), _ptr(out, _ip)))
         return out  # indexed [z, y, x]
 
 

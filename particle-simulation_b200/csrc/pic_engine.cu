@@ -1041,6 +1041,44 @@ int picb200_charge_box(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3
     CK(e, "Charge box");
     return 0;
 }
+// ---- picb200_charge_box without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// k_pack_box needs a contiguous scratch buffer for the box; here that scratch is a file-scope device array of a fixed,
+// modest size -- PICB200_NOALLOC_MAX_CELLS cells = 4 MiB, held by every GPU that loads the library until the process
+// exits.  In host code the array's NAME is only a host-side stand-in, not a device address: its device address is asked
+// for once per device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernel gets.
+// Every call on a device shares the array, and it keeps the last call's contents: k_pack_box overwrites every cell of the
+// requested box before the copy reads it, so nothing has to start at zero -- but two calls that overlap on one GPU
+// (two host threads, two streams) race on it.
+}  // extern "C"
+static __device__ __align__(256) int g_noalloc_box_scratch[PICB200_NOALLOC_MAX_CELLS];
+static int* g_noalloc_box_ptr[64] = {nullptr};       // per device: the array's DEVICE address
+extern "C" {
+int picb200_charge_box_noalloc(picb200_sim* sim, const int32_t lo[3], const int32_t hi[3], int32_t* out) {
+    if (!sim || !lo || !hi || !out) return fail("null argument", "Charge box (no allocation)");
+    Sim& s = sim->s;
+    CK(cudaSetDevice(s.device), "Set device");
+    const int wx = hi[0] - lo[0] + 1, wy = hi[1] - lo[1] + 1, wz = hi[2] - lo[2] + 1;
+    if (wx <= 0 || wy <= 0 || wz <= 0 || lo[0] < 0 || lo[1] < 0 || lo[2] < 0 || hi[0] >= kGrid || hi[1] >= kGrid || hi[2] >= kGrid)
+        return fail("bad box", "Charge box (no allocation)");
+    const size_t cells = (size_t)wx * wy * wz;
+    if (cells > (size_t)PICB200_NOALLOC_MAX_CELLS)
+        return fail("box of " + std::to_string(cells) + " cells exceeds the fixed scratch of " + std::to_string(PICB200_NOALLOC_MAX_CELLS) +
+                    " cells (PICB200_NOALLOC_MAX_CELLS); use picb200_charge_box", "Charge box (no allocation)");
+    if (s.device < 0 || s.device >= 64) return fail("device ordinal out of range", "Charge box (no allocation)");
+    if (!g_noalloc_box_ptr[s.device]) {              // set-up, once per device, that device current
+        int* ptr = nullptr;
+        CK(cudaGetSymbolAddress((void**)&ptr, g_noalloc_box_scratch), "Charge box (no allocation): cudaGetSymbolAddress");
+        if (!ptr) return fail("no device address for the scratch array", "Charge box (no allocation)");
+        g_noalloc_box_ptr[s.device] = ptr;
+    }
+    int* scratch = g_noalloc_box_ptr[s.device];
+    k_pack_box<<<s.aux_blocks, 256, 0, s.stream>>>(s.grid[s.cur], scratch, lo[0], lo[1], lo[2], wx, wy, wz, 0);
+    CK_LAST("Charge box (no allocation)");
+    CK(cudaMemcpyAsync(out, scratch, cells * 4, cudaMemcpyDeviceToHost, s.stream), "Charge box (no allocation)");
+    CK(cudaStreamSynchronize(s.stream), "Charge box (no allocation)");
+    return 0;
+}
 int picb200_charge_bbox(picb200_sim* sim, int32_t lo[3], int32_t hi[3]) {
     Sim& s = sim->s;
     if (s.sync_state()) return 1;
