@@ -1365,6 +1365,8 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
                 atomicMin(&st->bbox_lo[nbox][threadIdx.x], s_box[threadIdx.x]);
                 atomicMax(&st->bbox_hi[nbox][threadIdx.x], s_box[3 + threadIdx.x]);
             }
+            if (a.trace && (threadIdx.x & 31) == 0 && threadIdx.x <= 64)      // (diagnostic stamps 8, 9, 11: warps 0, 1, 2 on their way to the barrier)
+                a.trace[((size_t)step * gridDim.x + blockIdx.x) * 16 + (threadIdx.x == 0 ? 8 : threadIdx.x == 32 ? 9 : 11)] = globaltimer_ns();
             grid_barrier(st, seq, [&]() {
                 const int unfinished = v->n_unfinished;
                 v->n_unfinished = 0;
