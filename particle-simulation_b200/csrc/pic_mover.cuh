@@ -480,9 +480,17 @@ __device__ __forceinline__ void red_global_add(int* p, int v) { asm volatile("re
 // has already seen, so the warp first tests its cells against the box as it stands (a stale read errs on the safe
 // side) and reduces its own extent only when some lane falls outside.
 __device__ __forceinline__ void deposit_lanes(int* __restrict__ grid, bool active, int ix, int iy, int iz, int lane, int* s_box) {
+#ifdef PIC_DEPOSIT_MATCH
     const unsigned cell = active ? (unsigned)cell_index(ix, iy, iz) : (0xffffffffu - (unsigned)lane);
     const unsigned peers = __match_any_sync(kFull, cell);
     if (active && lane == __ffs(peers) - 1) red_global_add(grid + cell, __popc(peers));
+#else
+    // One red per live lane.  (Round 1 merged lanes that hit the same cell with match.any first; the lanes of a chunk are
+    // uncorrelated in space -- 32 electrons among the 2e5 cells of the box share a cell in 0.2 % of the chunks -- so the
+    // pre-reduction saved nothing and its latency showed up as 6.5 % of the stall samples of the HBM-side corner.  Lanes
+    // that do share a cell are serialised by the L2's atomic unit, which is what happened to the merged red's peers anyway.)
+    if (active) red_global_add(grid + cell_index(ix, iy, iz), 1);
+#endif
     int4 b0;                                                                 // lo x y z, hi x
     int2 b1;                                                                 // hi y z
     const unsigned box_addr = (unsigned)__cvta_generic_to_shared(s_box);
@@ -624,14 +632,18 @@ __device__ __forceinline__ void lockstep_push(const MoverCtx& c, float& x, float
                                               const bool slot_ok, int& n_adopted) {
     const float dt = (float)1e-12, hdt = (float)(1e-12 / 2);      // src/pic.cu:371
     const float sim = (float)(kGrid * 1e-2);                      // Sim_Size, src/cell.cu:4
-    uint4 rnd = make_uint4(0, 0, 0, 0);
+    // The Philox block of the first step is worked out in front of the loop: it needs the id only, so its ~50 instructions
+    // run while the caller's field gather is still in flight (inside the loop they sat behind the loop header, and the
+    // first leapfrog FMA -- i.e. the whole warp -- waited out the gather's latency with nothing to do: 12 % of all stall
+    // samples on the HBM-side corner)
+    uint4 rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), (c.g0 + (unsigned)t_first) >> 2, kTagCollide), *c.keys);
     bool refresh = false;
     const bool was_alive = alive;
     int t_end = c.pt;                                             // !kAdopt: the last step this lane's electron is pushed in
 #pragma unroll 1
     for (int t = t_first; t <= c.pt; ++t) {
         const unsigned g = c.g0 + (unsigned)t;
-        if (t == t_first || (g & 3u) == 0u || (kAdopt && refresh)) {         // warp-uniform
+        if ((t != t_first && (g & 3u) == 0u) || (kAdopt && refresh)) {       // warp-uniform
             rnd = philox4x32_10(make_uint4((uint32_t)id, (uint32_t)(id >> 32), g >> 2, kTagCollide), *c.keys);
             refresh = false;
         }
