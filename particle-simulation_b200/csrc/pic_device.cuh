@@ -31,10 +31,10 @@ constexpr int kEdgeBytes = (kRows + 1) * 4;
 constexpr int kTableSmemBytes = ((kThrBytes + kEdgeBytes + 15) / 16) * 16;
 
 // The streaming instantiation of the fused kernel (small poisson_timestep, HBM-side) keeps only the first kStreamRows rows
-// of the tables in shared memory -- |v|^2 < 10^(-6 + 22 * 3072 / 10000) = 5.7 m^2/s^2, four orders of magnitude above what
+// of the tables in shared memory -- |v|^2 < 10^(-6 + 22 * 2048 / 10000) = 0.032 m^2/s^2, sixty times what
 // the BASELINE configurations reach -- and reads higher rows from the global image; the freed shared memory holds its
 // chunk pipeline.  Layout of a window of R rows: thr[R] (8 B each), edge[R or kRows + 1] (4 B each), then the cell bounds.
-constexpr int kStreamRows = 3072;
+constexpr int kStreamRows = 2048;
 __host__ __device__ constexpr int smem_edge_off(int R) { return R == kRows ? kThrBytes : R * 8; }
 __host__ __device__ constexpr int smem_bnd_off(int R) { return R == kRows ? kTableSmemBytes : R * 12; }
 

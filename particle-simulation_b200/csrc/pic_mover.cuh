@@ -785,25 +785,46 @@ __device__ __forceinline__ void stream_issue(const MoverCtx& c, int i0, int end,
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ void stream_wait_older() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void stream_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // kStream: the chunk's eight arrays were copied into the warp's shared-memory buffer `sb` by cp.async while the previous
 // chunk was pushed (stream_issue): lane-indexed words x y z vx vy vz ts, then the 64-bit ids.
 constexpr int kStreamWordsPerChunk = 9 * 32;
-template <bool kAdopt, bool kStream>
+constexpr int kStreamFieldWords = 4 * 32;                       // one float4 per lane: the prefetched field records of a chunk
+// kStream, dense plasma (per-cell field): the field records of a chunk whose arrays have landed in `sb` are fetched into the
+// warp's field buffer `fb` by cp.async as well -- cells from the buffered positions, one 16-byte record per live lane --
+// a whole chunk ahead of their use.  (Fetched when the chunk was pushed, the record's L2/HBM latency was the largest single
+// stall of the HBM-side corner: the chain position -> cell -> record -> first leapfrog FMA has nothing to overlap with.)
+__device__ __forceinline__ void stream_field_issue(const MoverCtx& c, const FusedCtx& f, int i0, int end, const uint32_t* sb, uint32_t* fb) {
+    const int i = i0 + c.lane;
+    if (i < end && (int)sb[192 + c.lane] != kDead) {
+        const int ix = cell_of_fast(__uint_as_float(sb[c.lane]), f.bnd), iy = cell_of_fast(__uint_as_float(sb[32 + c.lane]), f.bnd),
+                  iz = cell_of_fast(__uint_as_float(sb[64 + c.lane]), f.bnd);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(fb + 4 * c.lane)), "l"(f.F + cell_index(ix, iy, iz)) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+struct NoAfterLoad { __device__ __forceinline__ void operator()() const {} };
+// after_load (kStream): called once the chunk's buffered words are in registers, i.e. when its buffers may be refilled --
+// the caller issues the next prefetches there, in front of the pushes.  fb != nullptr: the field records were prefetched.
+template <bool kAdopt, bool kStream, class AfterLoad = NoAfterLoad>
 __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedCtx& f, int i0, int end, int& staged, unsigned& pushes, int& dead, int& npool,
-                                                 const uint32_t* sb = nullptr) {
+                                                 const uint32_t* sb = nullptr, const uint32_t* fb = nullptr, AfterLoad after_load = AfterLoad()) {
     constexpr int kSmemRows = kStream ? kStreamRows : kRows;
     const int i = i0 + c.lane;
     const bool in = i < end;
     float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f;
     unsigned long long id = 0;
     int ts = -1;
+    float4 pf = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool prefetched = kStream && fb != nullptr;        // uniform
     if (in) {
         if (kStream) {
             x = __uint_as_float(sb[c.lane]); y = __uint_as_float(sb[32 + c.lane]); z = __uint_as_float(sb[64 + c.lane]);
             vx = __uint_as_float(sb[96 + c.lane]); vy = __uint_as_float(sb[128 + c.lane]); vz = __uint_as_float(sb[160 + c.lane]);
             ts = (int)sb[192 + c.lane];
             id = reinterpret_cast<const unsigned long long*>(sb + 224)[c.lane];
+            if (prefetched) pf = reinterpret_cast<const float4*>(fb)[c.lane];      // (a lane without a live electron reads a stale record nobody uses)
         } else {
             x = __ldcg(c.s.x + i); y = __ldcg(c.s.y + i); z = __ldcg(c.s.z + i);
             vx = __ldcg(c.s.vx + i); vy = __ldcg(c.s.vy + i); vz = __ldcg(c.s.vz + i);
@@ -811,6 +832,7 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
             id = __ldcg(c.s.id + i);
         }
     }
+    if (kStream) { __syncwarp(); after_load(); }
     if (__any_sync(kFull, (ts != -1) & (ts != kDead))) {      // uploaded populations may carry other timestamps
         fused_chunk<false, kSmemRows>(c, f, i0, end, staged, pushes, dead);
         return;
@@ -818,12 +840,16 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
     const bool was_alive = in & (ts != kDead);                // holes of earlier Poisson steps stay in place (lazy compaction)
     // updateGrid + gridToParticles for this electron's own cell (src/grid_operations.cu:29-72)
     float ax = 0.f, ay = 0.f, az = 0.f;
-    const float x0 = x, y0 = y, z0 = z;
-    int ix = cell_of_fast(x, f.bnd), iy = cell_of_fast(y, f.bnd), iz = cell_of_fast(z, f.bnd);
-    if (was_alive) {
-        gather_field(f, ix, iy, iz, ax, ay, az);
-        if (f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
+    float x0 = x, y0 = y, z0 = z;
+    int ix = 0, iy = 0, iz = 0;
+    if (prefetched) {
+        ax = pf.x; ay = pf.y; az = pf.z;
+        x0 = __int_as_float(0x7fc00000);                      // the cell was worked out a chunk ago and not kept: the deposit works it out again
+    } else {
+        ix = cell_of_fast(x, f.bnd); iy = cell_of_fast(y, f.bnd); iz = cell_of_fast(z, f.bnd);
+        if (was_alive) gather_field(f, ix, iy, iz, ax, ay, az);
     }
+    if (was_alive && f.store_acc) { __stcg(c.s.ax + i, ax); __stcg(c.s.ay + i, ay); __stcg(c.s.az + i, az); }
     bool alive = was_alive;
     int n_adopted = 0;                                            // children this lane took over from their parents' lanes
     lockstep_push<false, kAdopt, kSmemRows>(c, x, y, z, vx, vy, vz, ax, ay, az, id, alive, 0, 1, staged, pushes, dead, in, n_adopted);
@@ -987,7 +1013,7 @@ __device__ __forceinline__ void fused_staged(const MoverCtx& c, const FusedCtx& 
 constexpr int kBndSmemBytes = ((kBndBytes + 15) / 16) * 16;
 constexpr int kAllTableBytes = kTableSmemBytes + kBndSmemBytes;
 __host__ __device__ constexpr int smem_tables_bytes(int R) { return smem_bnd_off(R) + kBndSmemBytes; }      // R == kRows: kAllTableBytes
-constexpr int kStreamBytesPerWarp = 2 * kStreamWordsPerChunk * 4;                        // two chunks in flight per warp
+constexpr int kStreamBytesPerWarp = (2 * kStreamWordsPerChunk + kStreamFieldWords) * 4;  // two chunks in flight per warp + one chunk's field records
 // per warp: the children stage (whose first bytes double as the peer exchange's row buffer: that runs between
 // barrier 1 and barrier 2, when every stage is empty) and the free-slot pool
 static_assert(kPushStageBytesPerWarp <= kStageBytesPerWarp, "the peer row buffer lives inside the children stage");
@@ -1130,7 +1156,7 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
     int* const push_stage = reinterpret_cast<int*>(c.stage);        // peer exchange only, while the stage is empty
     c.pool = reinterpret_cast<int*>(smem_raw + kTablesBytes + (blockDim.x >> 5) * kStageBytesPerWarp) + (threadIdx.x >> 5) * kPoolSlots;
     uint32_t* const sbuf = reinterpret_cast<uint32_t*>(smem_raw + kTablesBytes + (blockDim.x >> 5) * (kStageBytesPerWarp + kPoolSlots * 4)) +
-                           (threadIdx.x >> 5) * (2 * kStreamWordsPerChunk);      // kStream only: this warp's two chunk buffers
+                           (threadIdx.x >> 5) * (kStreamBytesPerWarp / 4);       // kStream only: this warp's two chunk buffers + field buffer
     volatile DevState* const v = st;
 
     // ---- what ONE thread per block fetches after each grid barrier (BlockBc): every thread asking L2 for
@@ -1291,16 +1317,18 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             __syncwarp();
             if (c.lane == 0) { __threadfence_block(); *(volatile int*)&s_quota[3] = step_tag; }
         }
-        auto take_ticket = [&]() {
-            int k = 0;
-            if (c.lane == 0) k = smem_fetch_add(&s_ticket, 1);
-            k = __shfl_sync(kFull, k, 0);
+        auto chunk_of_ticket = [&](int k) {                   // ticket k of this block -> global chunk (0x7fffffff: none left)
             if (k < k_free) return k * G + (int)blockIdx.x;
             while (*(volatile int*)&s_quota[3] != step_tag) __nanosleep(20);      // (ready long before anybody gets here)
             const int base = *(volatile int*)&s_quota[0];
             if (k < base) { const int chunk = k * G + (int)blockIdx.x; return chunk; }
             const int j = k - base;
             return j < *(volatile int*)&s_quota[2] ? *(volatile int*)&s_quota[1] + j : 0x7fffffff;
+        };
+        auto take_ticket = [&]() {
+            int k = 0;
+            if (c.lane == 0) k = smem_fetch_add(&s_ticket, 1);
+            return chunk_of_ticket(__shfl_sync(kFull, k, 0));
         };
         if (!kStream) {
             for (bool more = true; more || staged;) {
@@ -1312,22 +1340,48 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
                 if (staged >= a.drain_at || (!more && staged)) fused_staged<kSmemRows>(c, f, staged, pushes, dead, npool);
             }
         } else {
-            // the same loop with the chunk's loads issued one chunk ahead (one cp.async group per iteration, also when empty)
-            int cur_chunk = take_ticket(), b = 0;
-            bool have = cur_chunk < chunks;
-            if (have) stream_issue(c, cur_chunk << 5, hw0, sbuf);
-            while (have || staged) {
-                bool have_next = false;
-                if (have) {
-                    const int next_chunk = take_ticket();
-                    have_next = next_chunk < chunks;
-                    stream_issue(c, have_next ? next_chunk << 5 : hw0, hw0, sbuf + (b ^ 1) * kStreamWordsPerChunk);
+            // the same loop with the chunk's loads issued one chunk ahead and -- dense plasma -- its field records as soon as
+            // its positions have landed (cp.async groups in commit order: arrays k+1, field k | field k+1, arrays k+2 | ...;
+            // every iteration starts by waiting for all of them, issued a whole chunk's pushes ago).  Tickets are static
+            // here (warp w takes tickets w, w + 32, ...): children are rare at these poisson_timesteps, so there is nothing
+            // for a shared counter to even out, and its atomic + shuffle sat in every chunk's dependency chain.
+            uint32_t* const fbuf = sbuf + 2 * kStreamWordsPerChunk;
+            const bool pf = f.F != nullptr;                      // uniform over the grid
+            int tk = (int)(threadIdx.x >> 5);
+            auto take_static = [&]() { const int k = tk; tk += (int)(blockDim.x >> 5); return chunk_of_ticket(k); };
+            int cur_chunk = take_static(), next_chunk = 0x7fffffff, b = 0;
+            bool have = cur_chunk < chunks, have_next = false;
+            if (have) {
+                stream_issue(c, cur_chunk << 5, hw0, sbuf);
+                next_chunk = take_static();
+                have_next = next_chunk < chunks;
+                stream_issue(c, have_next ? next_chunk << 5 : hw0, hw0, sbuf + kStreamWordsPerChunk);
+                if (pf) {
                     stream_wait_older();
-                    fused_chunk_fast<false, true>(c, f, cur_chunk << 5, hw0, staged, pushes, dead, npool, sbuf + b * kStreamWordsPerChunk);
-                    cur_chunk = next_chunk;
+                    __syncwarp();
+                    stream_field_issue(c, f, cur_chunk << 5, hw0, sbuf, fbuf);
+                }
+            }
+            while (have || staged) {
+                if (have) {
+                    stream_wait_all();
+                    __syncwarp();
+                    const int this_chunk = cur_chunk;
+                    uint32_t* const sb_cur = sbuf + b * kStreamWordsPerChunk;
+                    uint32_t* const sb_nxt = sbuf + (b ^ 1) * kStreamWordsPerChunk;
+                    fused_chunk_fast<false, true>(c, f, this_chunk << 5, hw0, staged, pushes, dead, npool, sb_cur, pf ? fbuf : nullptr, [&]() {
+                        // this chunk is in registers: its buffers are free for the chunk after next / the next chunk's field
+                        if (pf) stream_field_issue(c, f, have_next ? next_chunk << 5 : hw0, hw0, sb_nxt, fbuf);
+                        cur_chunk = next_chunk;
+                        have = have_next;
+                        if (have_next) {
+                            next_chunk = take_static();
+                            have_next = next_chunk < chunks;
+                        }
+                        stream_issue(c, have_next ? next_chunk << 5 : hw0, hw0, sb_cur);
+                    });
                     b ^= 1;
                 }
-                have = have_next;
                 if (staged >= a.drain_at || (!have && staged)) fused_staged<kSmemRows>(c, f, staged, pushes, dead, npool);
             }
         }

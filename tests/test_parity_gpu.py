@@ -415,12 +415,16 @@ def test_per_cell_field_path_matches_oracle(engine, oracle, ratio, pt):
     assert_state_equal(d, o.download_sorted())
 
 
-@pytest.mark.parametrize("stream_steps,pt", [(0, 1), (3, 1), (3, 2), (3, 3), (16, 10)])
-def test_streaming_step_loop_matches_oracle(engine, oracle, monkeypatch, stream_steps, pt):
+@pytest.mark.parametrize("stream_steps,pt,field_ratio", [(0, 1, None), (3, 1, None), (3, 1, "-1"), (3, 2, None), (3, 3, None), (3, 3, "-1"), (16, 10, None)])
+def test_streaming_step_loop_matches_oracle(engine, oracle, monkeypatch, stream_steps, pt, field_ratio):
     """Small poisson_timestep: the fused kernel streams its chunks (cp.async double buffer, a shared-memory window of the
-    first 3072 table rows; k_poisson_fused kVariant 2).  PICB200_STREAM_STEPS moves the threshold (0: never; 16: also at
+    first 2048 table rows; k_poisson_fused kVariant 2).  PICB200_STREAM_STEPS moves the threshold (0: never; 16: also at
     poisson_timestep 10).  A third of the electrons is fast enough (|v|^2 > 5.7) to use table rows BEYOND the window,
-    which come from the global image.  Same bits as the oracle; ragged population (not a multiple of 32)."""
+    which come from the global image.  At 3.7 electrons per cell the per-cell field is on, so the field records are
+    prefetched a chunk ahead (stream_field_issue); PICB200_FIELD_RATIO=-1 runs the same loop with the six-point gather.
+    Same bits as the oracle; ragged population (not a multiple of 32)."""
+    if field_ratio is not None:
+        monkeypatch.setenv("PICB200_FIELD_RATIO", field_ratio)
     rows = np.zeros((10000, 2), dtype=np.float32)
     rows[:, 0] = 1.5 + (np.arange(10000) % 7) * 0.25          # every row different from its neighbours: a wrong row shows
     rows[:, 1] = 1.0 + (np.arange(10000) % 5) * 0.2
