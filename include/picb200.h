@@ -195,10 +195,14 @@ int picb200_save_state(picb200_sim* sim, const char* path, int32_t sorted_by_id)
 int picb200_load_state(picb200_sim* sim, const char* path);
 
 /* ---- multi-GPU over NVLink peer memory (no reference counterpart: device 0 is hard-coded, src/pic.cu:394)
- * With nranks > 1 the modes 30/33 kernel can exchange the charge grid itself, by reading the peers' local
- * grids through NVLink, so that a whole run stays one launch per GPU.  Every rank exports a handle, the
- * caller gathers the nranks handles in rank order (threads: shared array; processes: any all-gather) and
- * every rank connects.  Works across threads of one process (peer access) and across processes (CUDA IPC).
+ * With nranks > 1 the modes 30/33 kernel exchanges the charge grid itself, by adding the rows of its local
+ * grid into every rank's summed grid over NVLink, so that a whole run stays one launch per GPU.  Every rank
+ * exports a handle, the caller gathers the nranks handles in rank order (threads: shared array; processes: any
+ * all-gather) and every rank connects.  Works across threads of one process (peer access) and across processes
+ * of one node (CUDA IPC).  Where the GPUs sit behind an NVSwitch the adds go through a multicast object (one
+ * multimem.red reaches all ranks; PICB200_NVLS=0 keeps one bulk reduce-add per peer): rank 0 creates it in
+ * picb200_peer_export, the others take it over in picb200_peer_connect, which is therefore COLLECTIVE -- all
+ * ranks must be inside the call at the same time (it waits up to 60 s for the others).
  * Without this call the engine falls back to one NCCL all-reduce per Poisson step (needs nccl_unique_id). */
 #define PICB200_PEER_HANDLE_BYTES 256
 int picb200_peer_export(picb200_sim* sim, void* handle_out /* PICB200_PEER_HANDLE_BYTES */);

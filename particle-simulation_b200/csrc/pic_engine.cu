@@ -7,6 +7,7 @@
 // modes 31/32 keep the host round trips that define them in the reference.
 #include "pic_device.cuh"
 #include "pic_nccl.h"
+#include "pic_nvls.h"
 #include "../../include/picb200.h"
 
 #include <algorithm>
@@ -163,6 +164,15 @@ struct Sim {
     PeerArgs pa{};
     bool peer_connected = false;
     std::vector<void*> ipc_opened;
+    // ... with the reduction in the NVSwitch (pic_nvls.h): grids 0/1 are ONE virtual-memory allocation bound to a multicast object
+    bool nvls = false;
+    size_t nvls_bytes = 0;
+    CUmemGenericAllocationHandle nvls_mem = 0, nvls_mc = 0;
+    CUdeviceptr nvls_uc = 0, nvls_mv = 0;      // the rank's own mapping of its grids / the multicast mapping
+    bool nvls_mc_owner = false, nvls_bound = false;
+    int nvls_fd = -1;                          // rank 0: the exported descriptor of the multicast object
+    char nvls_shm[40] = {0};                   // rank 0: name of the set-up barrier's shared-memory segment
+    int nvls_alloc_grids();
     int peer_export(void* out);
     int peer_connect(const void* handles);
     // profiling: CUDA-event spans per phase on the launching stream + a count of kernel launches
@@ -250,6 +260,19 @@ void Sim::release() {
     if (h_pl) { cudaFreeHost(h_pl); h_pl = nullptr; }
     cudaFree(soa_base); soa_base = nullptr;
     cudaFree(park_base); park_base = nullptr;
+    if (nvls) {
+        DrvApi* d = drv_api();
+        if (d) {
+            if (nvls_mv) { d->cuMemUnmap_(nvls_mv, nvls_bytes); d->cuMemAddressFree_(nvls_mv, nvls_bytes); nvls_mv = 0; }
+            if (nvls_uc) { d->cuMemUnmap_(nvls_uc, nvls_bytes); d->cuMemAddressFree_(nvls_uc, nvls_bytes); nvls_uc = 0; }
+            if (nvls_mc) { d->cuMemRelease_(nvls_mc); nvls_mc = 0; }
+            if (nvls_mem) { d->cuMemRelease_(nvls_mem); nvls_mem = 0; }
+        }
+        if (nvls_fd >= 0) { close(nvls_fd); nvls_fd = -1; }
+        if (nvls_shm[0]) { shm_unlink(nvls_shm); nvls_shm[0] = 0; }
+        grid[0] = grid[1] = nullptr;
+        nvls = false;
+    }
     for (int g = 0; g < kGrids; ++g) { cudaFree(grid[g]); grid[g] = nullptr; }
     cudaFree(field); field = nullptr;
     cudaFree(holes); holes = nullptr;
@@ -353,8 +376,13 @@ int Sim::create(const picb200_config* c) {
     CK(cudaMalloc(&movers, list_cap * 4), "Minor alloc");
 
     // ---- charge grid 512^3 int32, zeroed once (src/pic.cu:448-450 allocates 2 GiB of 16-B cells)
+    // several ranks, peer transport: the two summed grids come from the virtual-memory API when the box can reduce in the
+    // NVSwitch (pic_nvls.h; PICB200_NVLS=0 keeps cudaMalloc and the per-peer bulk reduce-adds)
+    if (cfg.nranks > 1 && !cfg.nccl_unique_id && !(getenv("PICB200_NVLS") && atoi(getenv("PICB200_NVLS")) == 0)) {
+        if (nvls_alloc_grids()) return 1;
+    }
     for (int g = 0; g < kGrids; ++g) {
-        CK(cudaMalloc(&grid[g], (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
+        if (!grid[g]) CK(cudaMalloc(&grid[g], (size_t)kGrid * kGrid * kGrid * 4), "Grid alloc");
         CK(cudaMemsetAsync(grid[g], 0, (size_t)kGrid * kGrid * kGrid * 4, stream), "Grid alloc");
     }
 
@@ -426,9 +454,56 @@ struct PeerHandle {
     long long pid;
     void* raw[3];                    // summed grid 0, summed grid 1, sync block
     int sm_count;                    // blocks of the persistent kernel: every rank counts nranks x blocks arrivals per exchange
-    cudaIpcMemHandle_t ipc[3];
+    int nvls;                        // this rank's summed grids can be bound to a multicast object (pic_nvls.h)
+    cudaIpcMemHandle_t ipc_sync;
+    union {
+        cudaIpcMemHandle_t ipc_grid[2];          // !nvls: the summed grids as CUDA IPC handles
+        struct {                                 // nvls, rank 0: the multicast object and the set-up barrier
+            unsigned long long mc;               //   the handle itself (ranks inside rank 0's process)
+            int fd;                              //   its POSIX file descriptor in process `pid` (other processes: pidfd_getfd)
+            char shm[40];
+        } nv;
+    };
 };
 static_assert(sizeof(PeerHandle) <= PICB200_PEER_HANDLE_BYTES, "handle fits the ABI blob");
+
+#define CKD(call, where)                                                                 \
+    do {                                                                                 \
+        CUresult _r = (call);                                                            \
+        if (_r != CUDA_SUCCESS) return fail(drv_error(d, _r) + " (" #call ")", where);   \
+    } while (0)
+
+static constexpr size_t kGridBytes = (size_t)kGrid * kGrid * kGrid * 4;
+
+// grids 0 and 1 as one 1 GiB virtual-memory allocation, when the device can join a multicast object; otherwise nothing
+// happens and the caller falls back to cudaMalloc
+int Sim::nvls_alloc_grids() {
+    DrvApi* d = drv_api();
+    if (!d) return 0;
+    CUdevice dev;
+    if (d->cuDeviceGet_(&dev, device) != CUDA_SUCCESS) return 0;
+    int ok = 0;
+    if (d->cuDeviceGetAttribute_(&ok, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev) != CUDA_SUCCESS || !ok) return 0;
+    nvls_bytes = 2 * kGridBytes;
+    CUmemAllocationProp ap;
+    memset(&ap, 0, sizeof ap);
+    ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    ap.location.id = device;
+    ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    CKD(d->cuMemCreate_(&nvls_mem, nvls_bytes, &ap, 0), "Grid alloc (NVLS)");
+    nvls = true;
+    CKD(d->cuMemAddressReserve_(&nvls_uc, nvls_bytes, kGridBytes, 0, 0), "Grid alloc (NVLS)");
+    CKD(d->cuMemMap_(nvls_uc, nvls_bytes, 0, nvls_mem, 0), "Grid alloc (NVLS)");
+    CUmemAccessDesc ad;
+    ad.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    ad.location.id = device;
+    ad.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    CKD(d->cuMemSetAccess_(nvls_uc, nvls_bytes, &ad, 1), "Grid alloc (NVLS)");
+    grid[0] = reinterpret_cast<int*>(nvls_uc);
+    grid[1] = reinterpret_cast<int*>(nvls_uc + kGridBytes);
+    return 0;
+}
 
 int Sim::peer_export(void* out) {
     if (cfg.nranks < 2 || !psync) return fail("peer export needs nranks > 1", "Peer setup");
@@ -440,12 +515,38 @@ int Sim::peer_export(void* out) {
     h.pid = (long long)getpid();
     h.raw[0] = grid[0]; h.raw[1] = grid[1]; h.raw[2] = psync;
     h.sm_count = sm_count;
-    for (int k = 0; k < 3; ++k) CK(cudaIpcGetMemHandle(&h.ipc[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
+    h.nvls = nvls ? 1 : 0;
+    CK(cudaIpcGetMemHandle(&h.ipc_sync, psync), "Peer setup (cudaIpcGetMemHandle)");
+    if (!nvls) {
+        for (int k = 0; k < 2; ++k) CK(cudaIpcGetMemHandle(&h.ipc_grid[k], h.raw[k]), "Peer setup (cudaIpcGetMemHandle)");
+    } else if (cfg.rank == 0) {
+        DrvApi* d = drv_api();
+        if (!nvls_mc) {
+            CUmulticastObjectProp mp;
+            memset(&mp, 0, sizeof mp);
+            mp.numDevices = (unsigned)cfg.nranks;
+            mp.size = nvls_bytes;
+            mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+            CKD(d->cuMulticastCreate_(&nvls_mc, &mp), "Peer setup (multicast object)");
+            nvls_mc_owner = true;
+            CKD(d->cuMemExportToShareableHandle_(&nvls_fd, nvls_mc, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0), "Peer setup (multicast object)");
+            static std::atomic<int> serial{0};
+            snprintf(nvls_shm, sizeof nvls_shm, "/picb200-%lld-%d", h.pid, serial.fetch_add(1));
+            shm_unlink(nvls_shm);
+            ShmBarrier* b = shm_barrier_open(nvls_shm, true);
+            if (!b) return fail("cannot create the shared-memory segment of the set-up barrier", "Peer setup");
+            munmap(b, 4096);
+        }
+        h.nv.mc = (unsigned long long)nvls_mc;
+        h.nv.fd = nvls_fd;
+        memcpy(h.nv.shm, nvls_shm, sizeof h.nv.shm);
+    }
     memset(out, 0, PICB200_PEER_HANDLE_BYTES);
     memcpy(out, &h, sizeof(h));
     return 0;
 }
 
+// Collective: every rank of the job calls it at the same time (one host thread or process per rank).
 int Sim::peer_connect(const void* handles) {
     if (cfg.nranks < 2 || !psync) return fail("peer connect needs nranks > 1", "Peer setup");
     CK(cudaSetDevice(device), "Set device");
@@ -453,11 +554,15 @@ int Sim::peer_connect(const void* handles) {
     pa.rank = cfg.rank;
     pa.nranks = cfg.nranks;
     pa.pl = pl;
+    PeerHandle h0;
+    memset(&h0, 0, sizeof h0);
     for (int r = 0; r < cfg.nranks; ++r) {
         PeerHandle h;
         memcpy(&h, static_cast<const unsigned char*>(handles) + (size_t)r * PICB200_PEER_HANDLE_BYTES, sizeof(h));
         if (h.magic != 0x50494342u) return fail("bad peer handle", "Peer setup");
         if (h.sm_count != sm_count) return fail("the ranks' GPUs have different SM counts (the exchange counts one arrival per block of every rank)", "Peer setup");
+        if ((h.nvls != 0) != nvls) return fail("the ranks disagree about the NVSwitch reduction (set PICB200_NVLS=0 on every rank)", "Peer setup");
+        if (r == 0) h0 = h;
         void* p[3] = {nullptr, nullptr, nullptr};
         if (r == cfg.rank) {
             p[0] = grid[0]; p[1] = grid[1]; p[2] = psync;
@@ -468,19 +573,64 @@ int Sim::peer_connect(const void* handles) {
             cudaError_t e = cudaDeviceEnablePeerAccess(h.device, 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(cudaGetErrorString(e), "Peer setup (enable peer access)");
             cudaGetLastError();
-            for (int k = 0; k < 3; ++k) p[k] = h.raw[k];
+            p[2] = h.raw[2];
+            if (!nvls) { p[0] = h.raw[0]; p[1] = h.raw[1]; }
         } else {
-            for (int k = 0; k < 3; ++k) {
-                CK(cudaIpcOpenMemHandle(&p[k], h.ipc[k], cudaIpcMemLazyEnablePeerAccess), "Peer setup (cudaIpcOpenMemHandle)");
+            CK(cudaIpcOpenMemHandle(&p[2], h.ipc_sync, cudaIpcMemLazyEnablePeerAccess), "Peer setup (cudaIpcOpenMemHandle)");
+            ipc_opened.push_back(p[2]);
+            for (int k = 0; k < 2 && !nvls; ++k) {
+                CK(cudaIpcOpenMemHandle(&p[k], h.ipc_grid[k], cudaIpcMemLazyEnablePeerAccess), "Peer setup (cudaIpcOpenMemHandle)");
                 ipc_opened.push_back(p[k]);
             }
         }
-        pa.sum[r][0] = static_cast<int*>(p[0]);
+        pa.sum[r][0] = static_cast<int*>(p[0]);          // nvls: the peers' grids are reached through the multicast mapping only
         pa.sum[r][1] = static_cast<int*>(p[1]);
         pa.sync[r] = static_cast<PeerSync*>(p[2]);
     }
     // connect before the first population is created (the grids are still all-zero then)
     if (charge_valid) return fail("picb200_peer_connect must precede the first Poisson step", "Peer setup");
+    if (nvls && !nvls_bound) {
+        DrvApi* d = drv_api();
+        CUdevice dev;
+        CKD(d->cuDeviceGet_(&dev, device), "Peer setup (multicast object)");
+        if (cfg.rank != 0) {
+            if (h0.pid == (long long)getpid()) {
+                nvls_mc = (CUmemGenericAllocationHandle)h0.nv.mc;          // (released by rank 0's Sim)
+            } else {
+                const int fd = steal_fd(h0.pid, h0.nv.fd);
+                if (fd < 0) return fail("cannot duplicate the multicast object's file descriptor out of rank 0's process (pidfd_getfd)", "Peer setup");
+                CUresult r = d->cuMemImportFromShareableHandle_(&nvls_mc, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+                close(fd);
+                if (r != CUDA_SUCCESS) return fail(drv_error(d, r) + " (cuMemImportFromShareableHandle)", "Peer setup (multicast object)");
+                nvls_mc_owner = true;
+            }
+        }
+        ShmBarrier* bar = shm_barrier_open(h0.nv.shm, false);
+        if (!bar) return fail("cannot open the shared-memory segment of the set-up barrier", "Peer setup");
+        CKD(d->cuMulticastAddDevice_(nvls_mc, dev), "Peer setup (multicast object)");
+        if (!shm_barrier_wait(bar, 0, cfg.nranks)) return fail("the ranks did not all reach picb200_peer_connect (it is collective)", "Peer setup");
+        CKD(d->cuMulticastBindMem_(nvls_mc, 0, nvls_mem, 0, nvls_bytes, 0), "Peer setup (multicast bind)");
+        CKD(d->cuMemAddressReserve_(&nvls_mv, nvls_bytes, kGridBytes, 0, 0), "Peer setup (multicast map)");
+        CKD(d->cuMemMap_(nvls_mv, nvls_bytes, 0, nvls_mc, 0), "Peer setup (multicast map)");
+        CUmemAccessDesc ad;
+        ad.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        ad.location.id = device;
+        ad.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        CKD(d->cuMemSetAccess_(nvls_mv, nvls_bytes, &ad, 1), "Peer setup (multicast map)");
+        if (!shm_barrier_wait(bar, 1, cfg.nranks)) return fail("the ranks did not all bind their grids", "Peer setup");
+        munmap(bar, 4096);
+        if (cfg.rank == 0) {
+            shm_unlink(nvls_shm); nvls_shm[0] = 0;
+            close(nvls_fd); nvls_fd = -1;
+        } else if (!nvls_mc_owner) {
+            nvls_mc = 0;                                                    // rank 0's handle: mapped here, released there
+        }
+        nvls_bound = true;
+    }
+    if (nvls) {
+        pa.mc[0] = reinterpret_cast<int*>(nvls_mv);
+        pa.mc[1] = reinterpret_cast<int*>(nvls_mv + kGridBytes);
+    }
     pa.debug = getenv("PICB200_PEER_DEBUG") ? atoi(getenv("PICB200_PEER_DEBUG")) : 0;
     pa.strict = (getenv("PICB200_PEER_FENCE") && !strcmp(getenv("PICB200_PEER_FENCE"), "sys")) ? 1 : 0;
     peer_connected = true;

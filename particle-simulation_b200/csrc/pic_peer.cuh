@@ -58,6 +58,7 @@ struct PeerArgs {
     int rank, nranks;
     PeerSync* sync[kMaxRanks];      // sync block of rank r as mapped into this GPU's address space (own rank: local pointer)
     int* sum[kMaxRanks][2];         // summed grids S[0], S[1] of rank r, likewise
+    int* mc[2];                     // S[0], S[1] of ALL ranks at once: the multicast mapping (NVSwitch reduction, pic_nvls.h), or nullptr
     PeerLocal* pl;
     int strict;                     // PICB200_PEER_FENCE=sys: system-scope fences around the arrival (see above)
     int debug;                      // PICB200_PEER_DEBUG (timing experiments only, results are wrong): 1 = skip the add into the own grid, 2 = skip the adds into the peers' grids
@@ -114,6 +115,27 @@ __device__ __forceinline__ void peer_add_rows(const PeerArgs& P, int p, int* __r
     const int lx = box[0] & ~3, hx = box[3] | 3;
     const int wx = hx - lx + 1, wy = box[4] - box[1] + 1, wz = box[5] - box[2] + 1;
     const int rows = wy * wz;
+    if (P.mc[p]) {
+        // NVSwitch reduction: one multimem.red per pair of cells adds them into the summed grid of EVERY rank (this one
+        // included) -- the row leaves this GPU once, the switch fans it out.  Two 32-bit counts travel as one 64-bit add:
+        // the low count cannot carry into the high one (a cell never holds 2^32 electrons).  Fire and forget: the
+        // block's arrival (peer_arrive) is preceded by a system-scope fence that covers these.
+        int* const M = P.mc[p];
+        for (int r = gw; r < rows; r += nw) {
+            const int y = box[1] + r % wy, z = box[2] + r / wy;
+            const size_t base = cell_index(lx, y, z);
+            for (int x0 = 2 * lane; x0 < wx; x0 += 64) {
+                int2* src = reinterpret_cast<int2*>(L + base + x0);
+                const int2 v = __ldcg(src);
+                if (v.x | v.y) {
+                    __stcg(src, make_int2(0, 0));                            // resetGrid of the local grid, on the way
+                    const unsigned long long w = (unsigned long long)(unsigned)v.x | ((unsigned long long)(unsigned)v.y << 32);
+                    asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(M + base + x0), "l"(w) : "memory");
+                }
+            }
+        }
+        return;
+    }
     const unsigned stage_addr = (unsigned)__cvta_generic_to_shared(stage);
     for (int r = gw; r < rows; r += nw) {
         const int y = box[1] + r % wy, z = box[2] + r / wy;
@@ -159,7 +181,7 @@ __device__ __forceinline__ void peer_send_box(const PeerArgs& P, unsigned e, con
 // of the old summed grid: this block's contribution to exchange `e` is complete.
 __device__ __forceinline__ void peer_arrive(const PeerArgs& P, unsigned e) {
     const int p = (int)(e & 1u);
-    if (P.strict) __threadfence_system();
+    if (P.strict || P.mc[p]) __threadfence_system();             // (multimem.red has no completion to wait for: the fence is the wait)
     for (int k = 1; k < P.nranks; ++k) red_relaxed_sys_add(&P.sync[(P.rank + k) % P.nranks]->arrive[p], 1u);
     red_release_gpu_add(&P.sync[P.rank]->arrive[p], 1u);        // the block's plain stores (rows of L and of the old grid zeroed) before its own rank goes on
 }

@@ -63,10 +63,15 @@ def need_gpus(engine, k):
         pytest.skip(f"needs {k} CUDA devices, {engine.device_count()} visible")
 
 
-@pytest.mark.parametrize("transport,pt", [("peer", 10), ("nccl", 10), ("peer", 32)])      # pt 32: the adopting step loop
+# "peer": rows added into every rank's summed grid inside the kernel -- through the NVSwitch (one multimem.red per pair of
+# cells, csrc/pic_nvls.h) where the box has one, else / "peer-unicast" (PICB200_NVLS=0) by one TMA bulk reduce-add per peer
+@pytest.mark.parametrize("transport,pt", [("peer", 10), ("peer-unicast", 10), ("nccl", 10), ("peer", 32)])      # pt 32: the adopting step loop
 @pytest.mark.parametrize("k", [2])
-def test_slabs_equal_single_population_oracle(engine, oracle, transport, pt, k):
+def test_slabs_equal_single_population_oracle(engine, oracle, monkeypatch, transport, pt, k):
     need_gpus(engine, k)
+    if transport == "peer-unicast":
+        monkeypatch.setenv("PICB200_NVLS", "0")
+        transport = "peer"
     n, cap = 40000, 800000
     rng = np.random.default_rng(3)
     pos = rng.uniform(2.45, 2.65, size=(3, n)).astype(np.float32)     # dense: ~5 electrons per cell, real fields
@@ -89,10 +94,11 @@ def test_slabs_equal_single_population_oracle(engine, oracle, transport, pt, k):
     assert c["added"] > 1000 and c["removed"] > 1000
 
 
-@pytest.mark.parametrize("k", [2, 4, 8])
-def test_peer_mode_equals_single_gpu_run(engine, k):
+@pytest.mark.parametrize("k,nvls", [(2, "1"), (4, "1"), (8, "1"), (8, "0")])
+def test_peer_mode_equals_single_gpu_run(engine, monkeypatch, k, nvls):
     """cfg1-shaped run (collision free) and a short colliding run: k slabs == 1 GPU, after sorting by id."""
     need_gpus(engine, k)
+    monkeypatch.setenv("PICB200_NVLS", nvls)
     n, pt, cap, P = 64000, 10, 1024000, 12
     with engine.Sim(mode=0, capacity=cap, poisson_timestep=pt, poisson_steps=P) as one:
         one.init_uniform(n)
