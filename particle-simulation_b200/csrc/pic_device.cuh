@@ -239,66 +239,7 @@ __global__ void k_init_uniform(Soa s, DevState* st, int init_n, unsigned long lo
     if (blockIdx.x == 0 && threadIdx.x == 0) { st->n = init_n; st->n_alloc = init_n; }
 }
 
-// ------------------------------------------------------------------------------------------
-// K_deposit: particlesToGrid (src/grid_operations.cu:15-26).  Nearest-grid-point count with
-// warp-level pre-reduction (__match_any_sync groups lanes that hit the same cell; one
-// red.global.add per group) and a block-reduced cell bounding box.
-// ------------------------------------------------------------------------------------------
-__global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge, int which) {
-    __shared__ int s_lo[3], s_hi[3];
-    if (threadIdx.x < 3) { s_lo[threadIdx.x] = kGrid; s_hi[threadIdx.x] = -1; }
-    __syncthreads();
-    const int n = st->n;
-    const int lane = threadIdx.x & 31;
-    const int rounded = (n + 31) & ~31;
-    int lx = kGrid, ly = kGrid, lz = kGrid, hx = -1, hy = -1, hz = -1;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += gridDim.x * blockDim.x) {
-        const bool in = i < n;
-        unsigned cell = 0xffffffffu - (unsigned)lane;          // unique per lane when inactive
-        if (in) {
-            int ix = cell_of(__ldcg(s.x + i)), iy = cell_of(__ldcg(s.y + i)), iz = cell_of(__ldcg(s.z + i));
-            cell = (unsigned)cell_index(ix, iy, iz);
-            lx = min(lx, ix); ly = min(ly, iy); lz = min(lz, iz);
-            hx = max(hx, ix); hy = max(hy, iy); hz = max(hz, iz);
-        }
-        const unsigned peers = __match_any_sync(kFull, cell);
-        if (in && lane == __ffs(peers) - 1) atomicAdd(charge + cell, __popc(peers));
-    }
-    lx = __reduce_min_sync(kFull, lx); ly = __reduce_min_sync(kFull, ly); lz = __reduce_min_sync(kFull, lz);
-    hx = __reduce_max_sync(kFull, hx); hy = __reduce_max_sync(kFull, hy); hz = __reduce_max_sync(kFull, hz);
-    if (lane == 0 && hx >= 0) {
-        atomicMin(&s_lo[0], lx); atomicMin(&s_lo[1], ly); atomicMin(&s_lo[2], lz);
-        atomicMax(&s_hi[0], hx); atomicMax(&s_hi[1], hy); atomicMax(&s_hi[2], hz);
-    }
-    __syncthreads();
-    if (threadIdx.x < 3 && s_hi[threadIdx.x] >= 0) {
-        atomicMin(&st->bbox_lo[which][threadIdx.x], s_lo[threadIdx.x]);
-        atomicMax(&st->bbox_hi[which][threadIdx.x], s_hi[threadIdx.x]);
-    }
-}
-
-// ------------------------------------------------------------------------------------------
-// K_gather: updateGrid + gridToParticles fused (src/grid_operations.cu:29-72).  Each electron
-// differences the six neighbour counts of its own cell: acc = float(EFC * double(c+ - c-)),
-// absent neighbours at the domain faces count as 0.  Bit-identical to computing the per-cell
-// field first, without the 12 B/cell field array or any whole-grid pass.
-// ------------------------------------------------------------------------------------------
-__global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ charge, double efc) {
-    const int n = st->n;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const int ix = cell_of(__ldcg(s.x + i)), iy = cell_of(__ldcg(s.y + i)), iz = cell_of(__ldcg(s.z + i));
-        const int* c = charge + cell_index(ix, iy, iz);
-        const int xm = (ix != 0) ? __ldg(c - 1) : 0;
-        const int xp = (ix != kGrid - 1) ? __ldg(c + 1) : 0;
-        const int ym = (iy != 0) ? __ldg(c - kGrid) : 0;
-        const int yp = (iy != kGrid - 1) ? __ldg(c + kGrid) : 0;
-        const int zm = (iz != 0) ? __ldg(c - kGrid * kGrid) : 0;
-        const int zp = (iz != kGrid - 1) ? __ldg(c + kGrid * kGrid) : 0;
-        __stcg(s.ax + i, __double2float_rn(__dmul_rn(efc, (double)(xp - xm))));
-        __stcg(s.ay + i, __double2float_rn(__dmul_rn(efc, (double)(yp - ym))));
-        __stcg(s.az + i, __double2float_rn(__dmul_rn(efc, (double)(zp - zm))));
-    }
-}
+// (k_deposit, k_field_box and k_gather of modes 31/32 and the phase-level ABI: pic_mover.cuh, next to the fused kernel's forms)
 
 // K_clear: resetGrid (src/grid_operations.cu:6-12) restricted to the deposited bounding box.
 // Warp-granular form for the fused kernel: global warp `gw` of `nw` empties its x-rows of the box.

@@ -407,7 +407,7 @@ int Sim::create(const picb200_config* c) {
     if (const char* fr = getenv("PICB200_FIELD_RATIO")) field_ratio = atoi(fr);
     // several ranks: the pass over the union box and its grid barrier are paid per rank whatever the slab holds: large slabs only
     field_min_n = getenv("PICB200_FIELD_MIN_N") ? atoi(getenv("PICB200_FIELD_MIN_N")) : (cfg.nranks > 1 ? 3000000 : 0);
-    if (fused && field_ratio >= 0 && (cfg.nranks == 1 || !cfg.nccl_unique_id))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
+    if (field_ratio >= 0 && (cfg.nranks == 1 || (fused && !cfg.nccl_unique_id)))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
         CK(cudaMalloc(&field, (size_t)kGrid * kGrid * kGrid * sizeof(float4)), "Grid alloc");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
@@ -680,7 +680,7 @@ int Sim::init_uniform(int init_n, unsigned long long id_base) {
 // ---- grid phase (src/pic.cu:501-504) ---------------------------------------------------------
 int Sim::op_deposit() {
     span_begin(kPhDeposit);
-    k_deposit<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], cur);
+    k_deposit<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], cur, tables + kTableSmemBytes / 4);
     charge_valid = true;
     ++launches;
     span_end();
@@ -695,7 +695,10 @@ int Sim::op_deposit() {
 }
 int Sim::op_gather() {
     span_begin(kPhGather);
-    k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc);
+    // dense plasma (decided on the device): the field once per cell of the occupied box, then one record per electron
+    float4* const F = (cfg.nranks == 1) ? field : nullptr;
+    if (F) { k_field_box<<<aux_blocks, 256, 0, stream>>>(st, grid[cur], F, efc, cur, field_ratio); ++launches; }
+    k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, F, cur, field_ratio);
     ++launches;
     span_end();
     CK_LAST("Gather");

@@ -610,6 +610,112 @@ __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, 
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// The grid phase as kernels of its own (modes 31/32, the phase-level ABI, the first deposit of a population).
+// Round 2: same cell index (single probe of the boundary table, staged in shared memory) and same two gathers as the
+// fused kernel -- round 1 ran the reference's double division three times per electron in each of them and always
+// took the six-point gather: 190 + 254 us per Poisson step of 1e7 electrons, against 214 us for the whole fused step.
+// ------------------------------------------------------------------------------------------
+constexpr int kGridPhaseUnroll = 4;
+// dense plasma, decided on the device from words every block reads alike: the box of grid `which` and n
+__device__ __forceinline__ bool box_is_dense(const DevState* st, int which, int ratio, int* box /* out: lo xyz, hi xyz */) {
+    for (int k = 0; k < 3; ++k) { box[k] = ld_volatile_i32(&st->bbox_lo[which][k]); box[3 + k] = ld_volatile_i32(&st->bbox_hi[which][k]); }
+    const long long cells = (long long)max(0, box[3] - box[0] + 1) * max(0, box[4] - box[1] + 1) * max(0, box[5] - box[2] + 1);
+    return ratio >= 0 && cells > 0 && (long long)ld_volatile_i32(&st->n) >= (long long)ratio * cells;
+}
+__device__ __forceinline__ void stage_cell_bounds(float* s_bnd, const float* __restrict__ g_bnd) {
+    for (int k = threadIdx.x; k <= kGrid; k += blockDim.x) s_bnd[k] = __ldg(g_bnd + k);
+    __syncthreads();
+}
+// K_deposit: particlesToGrid (src/grid_operations.cu:15-26).  Nearest-grid-point count, one red per electron, and a
+// block-reduced cell bounding box.
+__global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge, int which, const float* __restrict__ g_bnd) {
+    __shared__ int s_lo[3], s_hi[3];
+    __shared__ float s_bnd[kGrid + 1];
+    if (threadIdx.x < 3) { s_lo[threadIdx.x] = kGrid; s_hi[threadIdx.x] = -1; }
+    stage_cell_bounds(s_bnd, g_bnd);
+    const int n = st->n;
+    const int lane = threadIdx.x & 31;
+    int lx = kGrid, ly = kGrid, lz = kGrid, hx = -1, hy = -1, hz = -1;
+    // four electrons per thread and trip: twelve independent loads in flight (one per thread left the HBM idle half the time)
+    const int stride = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += kGridPhaseUnroll * stride) {
+        float px[kGridPhaseUnroll], py[kGridPhaseUnroll], pz[kGridPhaseUnroll];
+#pragma unroll
+        for (int u = 0; u < kGridPhaseUnroll; ++u) {
+            const int i = i0 + u * stride;
+            if (i < n) { px[u] = __ldcg(s.x + i); py[u] = __ldcg(s.y + i); pz[u] = __ldcg(s.z + i); }
+        }
+#pragma unroll
+        for (int u = 0; u < kGridPhaseUnroll; ++u) {
+            if (i0 + u * stride < n) {
+                const int ix = cell_of_fast(px[u], s_bnd), iy = cell_of_fast(py[u], s_bnd), iz = cell_of_fast(pz[u], s_bnd);
+                red_global_add(charge + cell_index(ix, iy, iz), 1);
+                lx = min(lx, ix); ly = min(ly, iy); lz = min(lz, iz);
+                hx = max(hx, ix); hy = max(hy, iy); hz = max(hz, iz);
+            }
+        }
+    }
+    lx = __reduce_min_sync(kFull, lx); ly = __reduce_min_sync(kFull, ly); lz = __reduce_min_sync(kFull, lz);
+    hx = __reduce_max_sync(kFull, hx); hy = __reduce_max_sync(kFull, hy); hz = __reduce_max_sync(kFull, hz);
+    if (lane == 0 && hx >= 0) {
+        atomicMin(&s_lo[0], lx); atomicMin(&s_lo[1], ly); atomicMin(&s_lo[2], lz);
+        atomicMax(&s_hi[0], hx); atomicMax(&s_hi[1], hy); atomicMax(&s_hi[2], hz);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 && s_hi[threadIdx.x] >= 0) {
+        atomicMin(&st->bbox_lo[which][threadIdx.x], s_lo[threadIdx.x]);
+        atomicMax(&st->bbox_hi[which][threadIdx.x], s_hi[threadIdx.x]);
+    }
+}
+// K_field_box: updateGrid (src/grid_operations.cu:29-56) over the occupied box of grid `which`, when the plasma is dense
+__global__ void k_field_box(const DevState* st, const int* __restrict__ charge, float4* __restrict__ F, double efc, int which, int ratio) {
+    int box[6];
+    if (!box_is_dense(st, which, ratio, box)) return;
+    field_rows(F, charge, box, efc, (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), (int)((gridDim.x * blockDim.x) >> 5), (int)(threadIdx.x & 31));
+}
+// K_gather: gridToParticles (src/grid_operations.cu:59-72) from the per-cell field of k_field_box, or -- sparse plasma --
+// updateGrid + gridToParticles for the electron's own cell: the six neighbour counts differenced on the spot,
+// acc = float(EFC * double(c+ - c-)), absent neighbours at the domain faces count 0.  Same expression, same bits.
+__global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ charge, double efc, const float* __restrict__ g_bnd,
+                         const float4* __restrict__ F, int which, int ratio) {
+    __shared__ float s_bnd[kGrid + 1];
+    stage_cell_bounds(s_bnd, g_bnd);
+    int box[6];
+    const bool dense = F != nullptr && box_is_dense(st, which, ratio, box);
+    const int n = st->n;
+    const int stride = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += kGridPhaseUnroll * stride) {
+        float px[kGridPhaseUnroll], py[kGridPhaseUnroll], pz[kGridPhaseUnroll];
+#pragma unroll
+        for (int u = 0; u < kGridPhaseUnroll; ++u) {
+            const int i = i0 + u * stride;
+            if (i < n) { px[u] = __ldcg(s.x + i); py[u] = __ldcg(s.y + i); pz[u] = __ldcg(s.z + i); }
+        }
+        if (dense) {
+            float4 v[kGridPhaseUnroll];
+#pragma unroll
+            for (int u = 0; u < kGridPhaseUnroll; ++u)
+                if (i0 + u * stride < n) v[u] = __ldcg(F + cell_index(cell_of_fast(px[u], s_bnd), cell_of_fast(py[u], s_bnd), cell_of_fast(pz[u], s_bnd)));
+#pragma unroll
+            for (int u = 0; u < kGridPhaseUnroll; ++u) {
+                const int i = i0 + u * stride;
+                if (i < n) { __stcg(s.ax + i, v[u].x); __stcg(s.ay + i, v[u].y); __stcg(s.az + i, v[u].z); }
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < kGridPhaseUnroll; ++u) {
+                const int i = i0 + u * stride;
+                if (i < n) {
+                    float ax, ay, az;
+                    gather_field_direct(charge, efc, cell_of_fast(px[u], s_bnd), cell_of_fast(py[u], s_bnd), cell_of_fast(pz[u], s_bnd), ax, ay, az);
+                    __stcg(s.ax + i, ax); __stcg(s.ay + i, ay); __stcg(s.az + i, az);
+                }
+            }
+        }
+    }
+}
+
 // generation-0 chunk of the fused kernel: gather from A, push, deposit into B
 // One electron per lane through mobility steps t_first..pt of the current Poisson step, the whole warp in
 // lockstep: all lanes run the same step t, so the loop is straight-line code -- the Philox block changes for
