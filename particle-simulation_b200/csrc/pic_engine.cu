@@ -140,6 +140,7 @@ struct Sim {
     int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
+    bool generic_ts = false;             // the population came with the caller's own timestamps (upload, state file): the next fused launch must handle any value
     int* holes = nullptr;
     int* movers = nullptr;
     size_t list_cap = 0;
@@ -649,6 +650,7 @@ int Sim::sync_state() {
     cur = h_st->cur;
     if (h_st->error == 2) return fail("more children waited for a compaction than the parking area holds", "Mobility phase");
     if (h_st->error == 3) return fail("a spilled child found no slot below the capacity", "Mobility phase");
+    if (h_st->error == 4) return fail("the streaming step loop met a timestamp other than -1 / DEAD", "Mobility phase");
     return collect_spans();
 }
 
@@ -865,7 +867,7 @@ int Sim::fused_steps(int steps) {
         span_begin(kPhMover);
         // which step loop: adopting from kAdoptMinSteps mobility steps per Poisson step, streaming up to kStreamMaxSteps (HBM-side)
         const bool adopt = cfg.poisson_timestep >= (getenv("PICB200_ADOPT_STEPS") ? atoi(getenv("PICB200_ADOPT_STEPS")) : kAdoptMinSteps);
-        const bool streaming = !adopt && mover_threads == 1024 && cfg.poisson_timestep <= (getenv("PICB200_STREAM_STEPS") ? atoi(getenv("PICB200_STREAM_STEPS")) : kStreamMaxSteps);
+        const bool streaming = !adopt && !generic_ts && mover_threads == 1024 && cfg.poisson_timestep <= (getenv("PICB200_STREAM_STEPS") ? atoi(getenv("PICB200_STREAM_STEPS")) : kStreamMaxSteps);
         const int variant = adopt ? 1 : (streaming ? 2 : 0);
         static const void* const kernels[2][3] = {{(const void*)k_poisson_fused<false, 0>, (const void*)k_poisson_fused<false, 1>, (const void*)k_poisson_fused<false, 2>},
                                                   {(const void*)k_poisson_fused<true, 0>, (const void*)k_poisson_fused<true, 1>, (const void*)k_poisson_fused<true, 2>}};
@@ -873,6 +875,7 @@ int Sim::fused_steps(int steps) {
                                        streaming ? (size_t)kFusedSmemBytes(mover_threads, true) : (size_t)kFusedSmemBytes(mover_threads) + fused_smem_pad, stream),
            "Mobility steps");
         ++launches; ++mover_launches;
+        generic_ts = false;              // a launch leaves every live electron at timestamp -1
         span_end();
         if (trace_path) {
             std::vector<unsigned long long> h(trace_words);
@@ -995,6 +998,7 @@ int picb200_upload(picb200_sim* sim, int32_t n, const float* x, const float* y, 
     }
     std::vector<int32_t> ts_def;
     std::vector<uint64_t> id_def;
+    s.generic_ts = ts != nullptr;
     if (!ts) { ts_def.assign((size_t)n, -1); ts = ts_def.data(); }
     if (!id) { id_def.resize((size_t)n); for (int i = 0; i < n; ++i) id_def[(size_t)i] = (uint64_t)i; id = id_def.data(); }
     CK(cudaMemcpyAsync(s.soa.ts, ts, (size_t)n * 4, cudaMemcpyHostToDevice, s.stream), "Upload");

@@ -940,8 +940,14 @@ __device__ __forceinline__ void fused_chunk_fast(const MoverCtx& c, const FusedC
     }
     if (kStream) { __syncwarp(); after_load(); }
     if (__any_sync(kFull, (ts != -1) & (ts != kDead))) {      // uploaded populations may carry other timestamps
-        fused_chunk<false, kSmemRows>(c, f, i0, end, staged, pushes, dead);
-        return;
+        if (kStream) {
+            // the host runs the first launch after an upload with the plain instantiation, which brings every timestamp to -1
+            // (this copy of the generic path cost the streaming loop 4.6 %); finding one here is a bug worth a loud failure
+            *(volatile int*)&c.st->error = 4;
+        } else {
+            fused_chunk<false, kSmemRows>(c, f, i0, end, staged, pushes, dead);
+            return;
+        }
     }
     const bool was_alive = in & (ts != kDead);                // holes of earlier Poisson steps stay in place (lazy compaction)
     // updateGrid + gridToParticles for this electron's own cell (src/grid_operations.cu:29-72)
@@ -1449,12 +1455,23 @@ __global__ void __launch_bounds__(1024, 1) k_poisson_fused(const __grid_constant
             // the same loop with the chunk's loads issued one chunk ahead and -- dense plasma -- its field records as soon as
             // its positions have landed (cp.async groups in commit order: arrays k+1, field k | field k+1, arrays k+2 | ...;
             // every iteration starts by waiting for all of them, issued a whole chunk's pushes ago).  Tickets are static
-            // here (warp w takes tickets w, w + 32, ...): children are rare at these poisson_timesteps, so there is nothing
-            // for a shared counter to even out, and its atomic + shuffle sat in every chunk's dependency chain.
+            // here (warp w takes tickets w, w + 32, ...) for most of the step: the shared counter's atomic + shuffle sat in every
+            // chunk's dependency chain.
             uint32_t* const fbuf = sbuf + 2 * kStreamWordsPerChunk;
             const bool pf = f.F != nullptr;                      // uniform over the grid
             int tk = (int)(threadIdx.x >> 5);
-            auto take_static = [&]() { const int k = tk; tk += (int)(blockDim.x >> 5); return chunk_of_ticket(k); };
+            const int nwb = (int)(blockDim.x >> 5);
+            const int k_static = (((chunks / G) * 3 / 4) / nwb) * nwb;      // ... for the first three quarters of an equal share; the
+            auto take_static = [&]() {                                      // rest is drawn from the shared counter, which evens out the tail
+                int k = tk;
+                if (k < k_static) {
+                    tk += nwb;
+                } else {
+                    if (c.lane == 0) k = k_static + smem_fetch_add(&s_ticket, 1);
+                    k = __shfl_sync(kFull, k, 0);
+                }
+                return chunk_of_ticket(k);
+            };
             int cur_chunk = take_static(), next_chunk = 0x7fffffff, b = 0;
             bool have = cur_chunk < chunks, have_next = false;
             if (have) {
