@@ -357,7 +357,9 @@ int Sim::create(const picb200_config* c) {
     soa.id = reinterpret_cast<unsigned long long*>(p);
     CK(cudaMemsetAsync(soa.ts, 0, f_bytes, stream), "Electron alloc");
     {
-        park_cap = (int)std::min<size_t>(cap, (size_t)1 << 20);
+        // the lazy compaction parks children when the slots above the holes run out before the reference's counter does; a
+        // forced compaction comes when one slot in eight is a hole, so an eighth of the capacity bounds what can wait
+        park_cap = (int)std::min<size_t>(cap, std::max<size_t>((size_t)1 << 20, cap / 8));
         const size_t pf = align_up((size_t)park_cap * 4, 256), pi = align_up((size_t)park_cap * 8, 256);
         CK(cudaMalloc(&park_base, pf * 10 + pi), "Electron alloc");
         unsigned char* q = static_cast<unsigned char*>(park_base);

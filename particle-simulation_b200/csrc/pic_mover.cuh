@@ -28,7 +28,7 @@ struct MoverArgs {
 
 // Children are staged per warp in shared memory: 12 words x kSS entries, field-major, so both the
 // ranked writes and the lane-indexed reads are bank-conflict free.  The unfused schedulers (k_mover) use the
-// first 32 entries; the fused kernel uses all 64, so that it can wait for enough children to make up a batch
+// first 32 entries; the fused kernel uses all kSS = 44, so that it can wait for enough children to make up a batch
 // of 32 with similar birth steps (fused_staged) -- a batch costs poisson_timestep - min(birth step) lockstep
 // steps whatever its lanes hold.
 constexpr int kStageWords = 12;
@@ -466,7 +466,9 @@ __device__ __forceinline__ int cell_of_fast(float p, const float* __restrict__ b
 
 // Atomics written as the single instruction they are: nvcc wraps an atomicAdd whose address it cannot prove distinct
 // per lane in its own warp-aggregation code (vote, leader election, popc, shuffle: ~15 instructions around one
-// ATOMS/ATOMG), which is pure overhead where the caller has already elected one lane.
+// ATOMS/ATOMG), which is pure overhead where the caller has already elected one lane.  (ptxas still does the same to
+// the shared-memory form under a lane predicate -- also to `atom.inc` with an unreachable bound, which it turns back into
+// an add; the global `red` is left alone.)
 __device__ __forceinline__ int smem_fetch_add(int* p, int v) {
     int old;
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
