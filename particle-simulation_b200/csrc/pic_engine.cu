@@ -137,6 +137,7 @@ struct Sim {
     float4* field = nullptr;             // fused kernel, one rank: dense per-cell field for dense plasmas (field_rows), 2 GiB
     int field_ratio = 2;                 // electrons per cell of the occupied box from which it is used (PICB200_FIELD_RATIO; < 0: never)
     int field_min_n = 0;                 // ... and electrons on this rank (PICB200_FIELD_MIN_N)
+    bool field_launch = false;           // modes 31/32: k_field_box is part of the grid phase (decided at create, see there)
     int* grid[kGrids] = {nullptr, nullptr, nullptr};   // three charge grids in rotation: gather from one, deposit the next step into the second, empty the third off the critical path
     int cur = 0;                         // host view of DevState::cur (valid after every sync)
     bool charge_valid = false;           // grid[cur] holds the deposit of the current population
@@ -309,6 +310,7 @@ int Sim::create(const picb200_config* c) {
     int bs = std::max(32, std::min(1024, (cfg.block_size / 32) * 32));
     blocks_per_sm = std::max(1, 1024 / bs);
     mover_threads = bs * blocks_per_sm;
+    if (const char* mt = getenv("PICB200_MOVER_THREADS")) mover_threads = std::max(32, std::min(1024, (atoi(mt) / 32) * 32));   // (experiments: how the fused kernel's rate depends on the warps per SM)
     aux_blocks = sm_count * 8;
     efc = (-1.602176487e-19 * -1.602176487e-19) / (4 * 3.1415926536 * 8.8541878176E-12 * 1e-2 * 1e-2 * 9.1093837015e-31);  // src/cell.cu:5
 
@@ -410,7 +412,11 @@ int Sim::create(const picb200_config* c) {
     if (const char* fr = getenv("PICB200_FIELD_RATIO")) field_ratio = atoi(fr);
     // several ranks: the pass over the union box and its grid barrier are paid per rank whatever the slab holds: large slabs only
     field_min_n = getenv("PICB200_FIELD_MIN_N") ? atoi(getenv("PICB200_FIELD_MIN_N")) : (cfg.nranks > 1 ? 3000000 : 0);
-    if (field_ratio >= 0 && (cfg.nranks == 1 || (fused && !cfg.nccl_unique_id)))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
+    // modes 31/32: the per-cell field is one more launch per Poisson step (18 us measured, whether it finds a dense plasma or
+    // not), which pays from about 2e6 electrons; the step's graph is captured once, so the configured population decides
+    field_launch = !fused && field_ratio >= 0 && cfg.nranks == 1 &&
+                   (getenv("PICB200_FIELD_LAUNCH") ? atoi(getenv("PICB200_FIELD_LAUNCH")) != 0 : cfg.init_n >= 2000000);
+    if (field_ratio >= 0 && ((cfg.nranks == 1 && (fused || field_launch)) || (cfg.nranks > 1 && fused && !cfg.nccl_unique_id)))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
         CK(cudaMalloc(&field, (size_t)kGrid * kGrid * kGrid * sizeof(float4)), "Grid alloc");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
@@ -700,7 +706,7 @@ int Sim::op_deposit() {
 int Sim::op_gather() {
     span_begin(kPhGather);
     // dense plasma (decided on the device): the field once per cell of the occupied box, then one record per electron
-    float4* const F = (cfg.nranks == 1) ? field : nullptr;
+    float4* const F = (cfg.nranks == 1 && field_launch) ? field : nullptr;
     if (F) { k_field_box<<<aux_blocks, 256, 0, stream>>>(st, grid[cur], F, efc, cur, field_ratio); ++launches; }
     k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, F, cur, field_ratio);
     ++launches;

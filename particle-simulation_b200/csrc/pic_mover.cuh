@@ -634,9 +634,10 @@ __device__ __forceinline__ void stage_cell_bounds(float* s_bnd, const float* __r
 __global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge, int which, const float* __restrict__ g_bnd) {
     __shared__ int s_lo[3], s_hi[3];
     __shared__ float s_bnd[kGrid + 1];
+    const int n = st->n;
+    if ((int)(blockIdx.x * blockDim.x) >= n) return;             // small populations: the other blocks stage nothing (whole block, before any barrier)
     if (threadIdx.x < 3) { s_lo[threadIdx.x] = kGrid; s_hi[threadIdx.x] = -1; }
     stage_cell_bounds(s_bnd, g_bnd);
-    const int n = st->n;
     const int lane = threadIdx.x & 31;
     int lx = kGrid, ly = kGrid, lz = kGrid, hx = -1, hy = -1, hz = -1;
     // four electrons per thread and trip: twelve independent loads in flight (one per thread left the HBM idle half the time)
@@ -674,7 +675,16 @@ __global__ void k_deposit(Soa s, DevState* st, int* __restrict__ charge, int whi
 __global__ void k_field_box(const DevState* st, const int* __restrict__ charge, float4* __restrict__ F, double efc, int which, int ratio) {
     int box[6];
     if (!box_is_dense(st, which, ratio, box)) return;
-    field_rows(F, charge, box, efc, (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), (int)((gridDim.x * blockDim.x) >> 5), (int)(threadIdx.x & 31));
+    // one thread per cell (field_rows' warp per x-row leaves this launch latency-bound: two dependent trips per warp)
+    const int lx = box[0], ly = box[1], lz = box[2];
+    const int wx = box[3] - lx + 1, wy = box[4] - ly + 1, wz = box[5] - lz + 1;
+    const int cells = wx * wy * wz;                              // <= 512^3 = 2^27
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < cells; k += gridDim.x * blockDim.x) {
+        const int x = lx + k % wx, r = k / wx, y = ly + r % wy, z = lz + r / wy;
+        float ax, ay, az;
+        gather_field_direct(charge, efc, x, y, z, ax, ay, az);
+        __stcg(F + cell_index(x, y, z), make_float4(ax, ay, az, 0.f));
+    }
 }
 // K_gather: gridToParticles (src/grid_operations.cu:59-72) from the per-cell field of k_field_box, or -- sparse plasma --
 // updateGrid + gridToParticles for the electron's own cell: the six neighbour counts differenced on the spot,
@@ -682,10 +692,11 @@ __global__ void k_field_box(const DevState* st, const int* __restrict__ charge, 
 __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ charge, double efc, const float* __restrict__ g_bnd,
                          const float4* __restrict__ F, int which, int ratio) {
     __shared__ float s_bnd[kGrid + 1];
+    const int n = st->n;
+    if ((int)(blockIdx.x * blockDim.x) >= n) return;
     stage_cell_bounds(s_bnd, g_bnd);
     int box[6];
     const bool dense = F != nullptr && box_is_dense(st, which, ratio, box);
-    const int n = st->n;
     const int stride = gridDim.x * blockDim.x;
     for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += kGridPhaseUnroll * stride) {
         float px[kGridPhaseUnroll], py[kGridPhaseUnroll], pz[kGridPhaseUnroll];

@@ -383,12 +383,15 @@ def test_children_batching_policy_matches_oracle(engine, oracle, drain_at, pt, s
 
 
 @pytest.mark.parametrize("ratio", [-1, 0, 1, 16])
-@pytest.mark.parametrize("pt", [1, 10])
-def test_per_cell_field_path_matches_oracle(engine, oracle, ratio, pt):
+@pytest.mark.parametrize("pt,mode", [(1, 0), (10, 0), (4, 1), (4, 2)])
+def test_per_cell_field_path_matches_oracle(engine, oracle, monkeypatch, ratio, pt, mode):
     """Dense plasmas: the fused kernel computes the field once per cell of the occupied box (field_rows, the
     reference's updateGrid, src/grid_operations.cu:29-56) and every electron fetches one record, instead of
     differencing six counts per electron.  PICB200_FIELD_RATIO (read at create) moves the density from which it
-    does: -1 never, 0 always, 1 and 16 electrons per cell (the population below has ~3).  Same bits."""
+    does: -1 never, 0 always, 1 and 16 electrons per cell (the population below has ~3).  Same bits.
+    Modes 31/32 (mode 1, 2 here) do the same with a kernel of their own (k_field_box) in front of the gather; it is
+    part of their grid phase from 2e6 configured electrons, PICB200_FIELD_LAUNCH=1 puts it there for this small one."""
+    monkeypatch.setenv("PICB200_FIELD_LAUNCH", "1")
     rows = np.tile(np.array([[3.0, 1.0]], dtype=np.float32), (10000, 1))
     rng = np.random.default_rng(77)
     n = 300000
@@ -397,7 +400,7 @@ def test_per_cell_field_path_matches_oracle(engine, oracle, ratio, pt):
     old = os.environ.get("PICB200_FIELD_RATIO")
     os.environ["PICB200_FIELD_RATIO"] = str(ratio)
     try:
-        with engine.Sim(capacity=8 * n, poisson_timestep=pt, mode=0, table_rows=rows, poisson_steps=5) as sim:
+        with engine.Sim(capacity=8 * n, poisson_timestep=pt, mode=mode, table_rows=rows, poisson_steps=5) as sim:
             sim.upload(*pos, *vel)
             sim.run_steps(2)
             sim.run_steps(3)
