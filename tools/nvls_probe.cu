@@ -27,6 +27,16 @@ __global__ void k_mc_add(int* mc, size_t n, int v) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         asm volatile("multimem.red.relaxed.sys.global.add.s32 [%0], %1;" ::"l"(mc + i), "r"(v) : "memory");
 }
+// reduce-scatter + all-gather through the switch: this rank pulls the sum over all replicas of its slice of `src`
+// (multimem.ld_reduce: the switch adds) and multicasts it into every replica of `dst` (multimem.st)
+__global__ void k_mc_rs_ag(const unsigned long long* mc_src, unsigned long long* mc_dst, size_t n64, int rank, int nranks) {
+    const size_t per = (n64 + nranks - 1) / nranks, lo = per * rank, hi = lo + per < n64 ? lo + per : n64;
+    for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+        unsigned long long v;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(v) : "l"(mc_src + i) : "memory");
+        asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(mc_dst + i), "l"(v) : "memory");
+    }
+}
 __global__ void k_check(const int* p, size_t n, int expect, unsigned long long* bad) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         if (p[i] != expect) atomicAdd(bad, 1ull);
@@ -123,6 +133,31 @@ int main(int argc, char** argv) {
     k_check<<<148, 1024>>>((const int*)uc, box, nranks * (nranks + 1) / 2 + nranks * reps, bad); CKR(cudaDeviceSynchronize());
     printf("[rank %d] after the timed adds: %llu wrong words\n", g_rank, *bad);
     barrier();
+    // reduce-scatter + all-gather: src = words [0, box) (every replica holds `fill` there), dst = words [box2, box2 + box)
+    {
+        const size_t box2 = 64ull << 20;          // 256 MiB further on
+        k_fill<<<592, 1024>>>((int*)uc, box, g_rank + 1); k_fill<<<592, 1024>>>((int*)uc + box2, box, 0); CKR(cudaDeviceSynchronize());
+        barrier();
+        k_mc_rs_ag<<<148, 1024>>>((const unsigned long long*)mv, (unsigned long long*)((int*)mv + box2), box / 2, g_rank, nranks); CKR(cudaDeviceSynchronize());
+        barrier();
+        *bad = 0;
+        k_check<<<148, 1024>>>((const int*)uc + box2, box, nranks * (nranks + 1) / 2, bad); CKR(cudaDeviceSynchronize());
+        printf("[rank %d] reduce-scatter + all-gather (ld_reduce + multimem.st): %llu wrong words\n", g_rank, *bad);
+        barrier();
+        CKR(cudaEventRecord(e0));
+        for (int i = 0; i < reps; ++i) k_mc_rs_ag<<<148, 1024>>>((const unsigned long long*)mv, (unsigned long long*)((int*)mv + box2), box / 2, g_rank, nranks);
+        CKR(cudaEventRecord(e1)); CKR(cudaDeviceSynchronize());
+        CKR(cudaEventElapsedTime(&ms, e0, e1));
+        printf("[rank %d] ld_reduce of a 1/%d slice of the 62^3 box + multimem.st of the result: %.2f us per launch, all ranks at once\n", g_rank, nranks, ms * 1e3 / reps);
+        barrier();
+        // for scale: an empty kernel launched the same way
+        CKR(cudaEventRecord(e0));
+        for (int i = 0; i < reps; ++i) k_fill<<<148, 1024>>>((int*)uc, 0, 0);
+        CKR(cudaEventRecord(e1)); CKR(cudaDeviceSynchronize());
+        CKR(cudaEventElapsedTime(&ms, e0, e1));
+        printf("[rank %d] empty kernel: %.2f us per launch\n", g_rank, ms * 1e3 / reps);
+        barrier();
+    }
     if (g_rank == 0) for (int r = 1; r < nranks; ++r) wait(nullptr);
     return 0;
 }
