@@ -5,9 +5,9 @@ Workload (N=1): BASELINE cfg2 = `run 30 0 1000000 100 256 100000000 100 10`: the
 scheduler (mode 30), 1e6 initial electrons, 100 Poisson steps x 10 mobility steps, capacity 1e8,
 shipped cross-section table.  One bench "step" = one complete run of that configuration (~1e9
 pushes).  N>1: every rank runs the same slab size (weak scaling, global init n = N x 1e6); the charge box is
-summed across the GPUs INSIDE the persistent kernel by bulk reduce-adds into the peers' memory over NVLink
-(csrc/pic_peer.cuh) -- no NCCL call on the data path (PICB200_NCCL=1 selects the one-all-reduce-per-Poisson-step
-fallback).  Before anything is timed, a run with N > 1 checks itself: a short colliding workload on the N slabs
+summed across the GPUs INSIDE the persistent kernel -- one multimem.red per pair of cells through the NVSwitch, or
+(PICB200_NVLS=0) one bulk reduce-add per peer over NVLink peer memory (csrc/pic_peer.cuh, csrc/pic_nvls.h) -- no NCCL
+call on the data path (PICB200_NCCL=1 selects the one-all-reduce-per-Poisson-step fallback).  Before anything is timed, a run with N > 1 checks itself: a short colliding workload on the N slabs
 must equal the same population on ONE GPU (counts and an order-independent digest of every electron) -> `parity_check`.
 
   value     pushes / device time of the Poisson loop (cudaEvent span, as src/pic.cu:476..:563),
@@ -22,6 +22,8 @@ must equal the same population on ONE GPU (counts and an order-independent diges
             figure may exceed the HBM peak; `traffic` is the DRAM traffic ncu measured for it (a committed capture,
             labelled with its commit -- not measured in this run).  `issue_frac` is the honest ceiling: pushes/s
             against 4 warp-instructions per SM and cycle / (warp-instructions per push, same capture).
+  roofline_hbm_corner  (N = 1) the same kernel where every push really crosses HBM, measured live: cfg5 with one push per
+            Poisson step, 1e7 electrons (> L2); there 68 B x pushes / time IS an HBM utilisation.
   cfg4      BASELINE configs[3]: 1e9 electrons in total sharded over the N GPUs, 10 x 10 steps, device-timed
             (strong scaling: the per-N values of this sub-record divide the same work).
   --impl reference   times the reference itself: its own CUDA program (oracle/_ref/main, built from
@@ -263,6 +265,28 @@ def cfg4_record(eng, dist, rank, world, local, uid, runs=3):
             "final_n": int(final_all), "pushes_per_run": int(pushes_all) // runs, "timing": "cudaEvent span of the Poisson loop on the engine's stream, max over ranks"}
 
 
+def hbm_corner_record(eng, local, peak, runs=3):
+    """The memory-side corner of the same kernel, measured live (N = 1): cfg5 with one push per Poisson step -- 1e7 electrons,
+    40 Poisson steps, every push really crosses HBM (the 480 MB population does not fit the 126 MB L2), so here the 68-B
+    figure IS an HBM utilisation.  Device-timed span of the Poisson loop (the first deposit, two steps of quota warm-up and
+    the closing compaction included), 1 warm-up + `runs` timed runs."""
+    kw = dict(mode=eng.MODE_DYNAMIC, init_n=10_000_000, poisson_steps=40, capacity=100_000_000, poisson_timestep=1, block_size=256, sleep_time_ns=100)
+    ms, pushes = [], 0
+    with eng.Sim(device=local, **kw) as sim:
+        sim.set_profiling(1)
+        for it in range(1 + runs):
+            sim.init_uniform(kw["init_n"], 0)
+            sim.run_steps(kw["poisson_steps"])
+            m = sim.summary()
+            if it > 0:
+                ms.append(m["gpu_ms"])
+                pushes += m["pushes"]
+    gbs = pushes * BYTES_PER_PUSH / (sum(ms) / 1e3) / 1e9
+    return {"workload": "cfg5-shaped, poisson_timestep = 1: run 30 0 10000000 40 256 100000000 100 1", "bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s",
+            "frac": gbs / peak if peak else None, "value": pushes / (sum(ms) / 1e3), "value_unit": UNIT, "ms_per_run": sum(ms) / len(ms), "us_per_poisson_step": 1e3 * sum(ms) / len(ms) / kw["poisson_steps"],
+            "runs": runs, "kernel": "k_poisson_fused (streaming instantiation)", "accounting": f"{BYTES_PER_PUSH:.0f} B per push x pushes / device time of the Poisson loop; inputs > L2"}
+
+
 def cpu_baseline(budget_s=12.0):
     """The CPU port (oracle/, OpenMP over all host cores) on a bounded sample of cfg2: its first
     Poisson steps until ~budget_s of wall time is used."""
@@ -401,6 +425,13 @@ def run_ours(args):
         dropin = {"value": dpush / sum(walls), "unit": UNIT, "wall_ms_per_run": 1e3 * sum(walls) / len(walls), "gpu_ms_last": sm.gpu_ms, "d2h_bytes_per_run": dn * 64,
                   "what": "picb200_run(): create (all device allocations) + init on the device + 100 Poisson steps + 64-byte AoS export (device transpose) into a pinned host buffer + destroy, wall clock; the reference's `GPU time of program` excludes its allocations"}
 
+    corner = None
+    if world == 1 and not os.environ.get("PICB200_BENCH_NO_CORNER"):
+        try:
+            corner = hbm_corner_record(eng, local, measured_hbm_peak()[0])
+        except eng.EngineError as e:
+            corner = {"error": str(e)}
+
     cfg4 = None
     if not os.environ.get("PICB200_BENCH_NO_CFG4"):
         try:
@@ -431,7 +462,7 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "per_gpu_init_n": n_local, "global_init_n": n_local * world, "final_n_rank0": final["final_n"],
                    "pushes_per_step_rank0": pushes // max(1, args.steps), "parallelism": (f"particle slabs x{world}, " + ("NCCL all-reduce of the charge box per Poisson step" if use_nccl else "charge box summed inside the persistent kernel over NVLink peer memory")) if world > 1 else "single GPU",
-                   "collective": ("ncclAllReduce(int32, sum) per Poisson step" if use_nccl else "none: in-kernel TMA bulk reduce-adds into the peers' memory over NVLink (no NCCL call on the data path)") if world > 1 else "none",
+                   "collective": ("ncclAllReduce(int32, sum) per Poisson step" if use_nccl else "none: in-kernel adds into every rank's summed grid (multimem.red through the NVSwitch, or PICB200_NVLS=0: TMA bulk reduce-adds into the peers' memory); no NCCL call on the data path") if world > 1 else "none",
                    "l2": "flushed after the population is initialised, before every timed run (512 MiB memset > 126 MB L2); the 48 MB working set then stays L2-resident within a run, as it does for the reference"},
         "e2e": {"value": e2e_pushes_all / e2e_max, "unit": UNIT, "h2d_bytes_per_step": n_local * 48, "d2h_bytes_per_step": d2h_bytes // max(1, args.steps),
                 "what": "picb200_upload (pinned host SoA) + picb200_run_steps + picb200_download (pinned host SoA), wall clock"},
@@ -447,6 +478,7 @@ def run_ours(args):
         "parity_check": parity,
         "e2e_dropin": dropin,
         "cfg4": cfg4,
+        "roofline_hbm_corner": corner,
         "phases_ms_per_step": {k: v for k, v in phases.items() if k.endswith("_ms")},
         "clocks": clocks,
     }

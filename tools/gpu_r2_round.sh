@@ -12,7 +12,7 @@ timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_ref
 python - <<PY
 import json
 d=json.loads(open("$O/bench.log").read().strip().splitlines()[-1]); r=json.loads(open("$O/bench_ref.log").read().strip().splitlines()[-1])
-print("ours value %.4g ms %.3f e2e %.4g issue_frac %s dropin %.4g | cfg4 %s | reference %.4g (%.1f ms) -> x%.1f device, x%.1f e2e" % (d["value"], d["ms_per_step"], d["e2e"]["value"], d["roofline"].get("issue_frac"), (d.get("e2e_dropin") or {}).get("value", 0), (d.get("cfg4") or {}).get("ms_per_run"), r["value"], r["ms_per_step"], d["value"]/r["value"], d["e2e"]["value"]/r["value"]))
+print("ours value %.4g ms %.3f e2e %.4g issue_frac %s dropin %.4g | hbm corner %s | cfg4 %s | reference %.4g (%.1f ms) -> x%.1f device, x%.1f e2e" % (d["value"], d["ms_per_step"], d["e2e"]["value"], d["roofline"].get("issue_frac"), (d.get("e2e_dropin") or {}).get("value", 0), (d.get("roofline_hbm_corner") or {}).get("frac"), (d.get("cfg4") or {}).get("ms_per_run"), r["value"], r["ms_per_step"], d["value"]/r["value"], d["e2e"]["value"]/r["value"]))
 PY
 # ---- ncu: launch list of the bench command (after the plain run above exited 0), then full captures
 PICB200_BENCH_NO_CPU=1 PICB200_BENCH_NO_CFG4=1 PICB200_BENCH_NO_DROPIN=1 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv python bench.py --steps 2 --warmup 3 > $O/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
