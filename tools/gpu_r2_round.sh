@@ -16,10 +16,12 @@ print("ours value %.4g ms %.3f e2e %.4g issue_frac %s dropin %.4g | hbm corner %
 PY
 # ---- ncu: launch list of the bench command (after the plain run above exited 0), then full captures
 PICB200_BENCH_NO_CPU=1 PICB200_BENCH_NO_CFG4=1 PICB200_BENCH_NO_DROPIN=1 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv python bench.py --steps 2 --warmup 3 > $O/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
+export PICB200_NO_WARM=1   # (the capture indices below count the launches of prof_run.py, not the zero-step warm-up launch of picb200_create)
 timeout 300 python tools/prof_run.py 0 1000000 10 10 4000000 30 > $O/plain_prof.log 2>&1 &&
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_poisson_fused -s 1 -c 1 -f -o $O/prof_fused python tools/prof_run.py 0 1000000 10 10 4000000 30 > $O/ncu_full.log 2>&1; echo "ncu full cfg2 rc=$?"
 timeout 300 python tools/prof_run.py 0 10000000 10 1 100000000 0 > $O/plain_prof_pt1.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_poisson_fused -c 1 -f -o $O/prof_pt1 python tools/prof_run.py 0 10000000 10 1 100000000 0 > $O/ncu_pt1.log 2>&1; echo "ncu full pt1 rc=$?"
+unset PICB200_NO_WARM
 # ---- phase traces
 PICB200_TRACE=$O/trace.bin python tools/prof_run.py 0 1000000 10 10 4000000 30 > $O/trace_run.log 2>&1; python tools/trace_summary.py $O/trace.bin > $O/trace_cfg2.txt 2>&1; head -6 $O/trace_cfg2.txt
 PICB200_TRACE=$O/trace_pt1.bin python tools/prof_run.py 0 10000000 10 1 100000000 0 > $O/trace_pt1_run.log 2>&1; python tools/trace_summary.py $O/trace_pt1.bin > $O/trace_pt1.txt 2>&1; head -6 $O/trace_pt1.txt
