@@ -176,11 +176,44 @@ def state_digest(d):
     return int(h.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(h)) if h.size else 0
 
 
-def connect_peers(dist, sim, world):
-    handles = [None] * world
-    dist.all_gather_object(handles, sim.peer_export())
-    sim.peer_connect(handles)
-    dist.barrier()
+PEER_TRANSPORT = {"kind": None, "note": None}     # what the last peer_sim() ended up with (for the bench line)
+
+
+def peer_sim(eng, dist, world, **kw):
+    """One rank's Sim with the in-kernel exchange wired up.  The exchange goes through the NVSwitch (a multicast object
+    shared between the ranks, csrc/pic_nvls.h) where the box offers it; should that set-up fail on ANY rank -- the ranks
+    agree on it over gloo after each phase -- every rank falls back to one bulk reduce-add per peer (PICB200_NVLS=0)
+    instead of failing the run."""
+    for attempt in (0, 1):
+        sim, handle, err = None, None, None
+        try:
+            sim = eng.Sim(**kw)
+            handle = sim.peer_export()
+        except eng.EngineError as e:
+            err = str(e)
+        handles = [None] * world
+        dist.all_gather_object(handles, (handle, err))
+        bad = [e for _, e in handles if e]
+        if not bad:
+            try:
+                sim.peer_connect([h for h, _ in handles])
+            except eng.EngineError as e:
+                err = str(e)
+            errs = [None] * world
+            dist.all_gather_object(errs, err)
+            bad = [e for e in errs if e]
+        if not bad:
+            nvls = os.environ.get("PICB200_NVLS", "1") not in ("0",)
+            PEER_TRANSPORT["kind"] = "peer (NVSwitch multicast where available)" if nvls else "peer (one bulk reduce-add per peer, PICB200_NVLS=0)"
+            dist.barrier()
+            return sim
+        if sim is not None:
+            sim.close()
+        if attempt == 1 or os.environ.get("PICB200_NVLS") == "0":
+            raise SystemExit("bench.py: peer set-up failed: " + bad[0])
+        os.environ["PICB200_NVLS"] = "0"
+        PEER_TRANSPORT["note"] = "NVSwitch set-up failed, fell back to one bulk reduce-add per peer: " + bad[0].strip().splitlines()[0]
+    raise SystemExit("bench.py: peer set-up failed")
 
 
 def parity_check(eng, dist, rank, world, local, uid):
@@ -195,9 +228,8 @@ def parity_check(eng, dist, rank, world, local, uid):
     pos = rng.uniform(2.45, 2.65, size=(3, n)).astype(np.float32)
     vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)
     lo, hi = n * rank // world, n * (rank + 1) // world
-    sim = eng.Sim(mode=0, capacity=cap // world, poisson_timestep=pt, poisson_steps=sum(steps), device=local, rank=rank, nranks=world, nccl_unique_id=uid)
-    if uid is None:
-        connect_peers(dist, sim, world)
+    kw = dict(mode=0, capacity=cap // world, poisson_timestep=pt, poisson_steps=sum(steps), device=local, rank=rank, nranks=world, nccl_unique_id=uid)
+    sim = peer_sim(eng, dist, world, **kw) if uid is None else eng.Sim(**kw)
     sim.upload(*[a[lo:hi] for a in pos], *[a[lo:hi] for a in vel], id=np.arange(lo, hi, dtype=np.uint64))
     dist.barrier()
     for k in steps:
@@ -222,7 +254,7 @@ def parity_check(eng, dist, rank, world, local, uid):
             m1 = one.summary()
             exp = [m1["final_n"], m1["total_added"], m1["total_removed"], m1["pushes"]] + list(state_digest(one.download()))
         res[0] = {"ok": got == exp, "n_initial": n, "final_n": got[0], "added": got[1], "removed": got[2], "pushes": got[3],
-                  "digest": "%016x:%016x" % (got[4], got[5]), "transport": "nccl" if uid is not None else "peer",
+                  "digest": "%016x:%016x" % (got[4], got[5]), "transport": "nccl" if uid is not None else "peer", "transport_detail": PEER_TRANSPORT["kind"] if uid is None else None, "transport_note": PEER_TRANSPORT["note"],
                   "what": f"{world} slabs vs the same population on one GPU: counts and (sum, xor) digest of (id, position, velocity) of every electron"}
         if not res[0]["ok"]:
             res[0]["expected"] = exp
@@ -239,9 +271,8 @@ def cfg4_record(eng, dist, rank, world, local, uid, runs=3):
     mobility steps, capacity 1.6e9 in total.  Device-timed, 1 warm-up + `runs` timed runs, max over ranks."""
     kw = dict(CFG4)
     kw["capacity"] = CFG4["capacity"] // world
-    sim = eng.Sim(device=local, rank=rank, nranks=world, nccl_unique_id=uid, **kw)
-    if world > 1 and uid is None:
-        connect_peers(dist, sim, world)
+    kw.update(device=local, rank=rank, nranks=world, nccl_unique_id=uid)
+    sim = peer_sim(eng, dist, world, **kw) if (world > 1 and uid is None) else eng.Sim(**kw)
     n = CFG4["init_n"]
     lo, hi = n * rank // world, n * (rank + 1) // world
     ms, pushes, final_n = [], 0, 0
@@ -330,9 +361,8 @@ def run_ours(args):
     n_local = CFG2["init_n"]
     kw = dict(CFG2)
     kw["init_n"] = n_local * world
-    sim = eng.Sim(device=local, rank=rank, nranks=world, nccl_unique_id=uid, **kw)
-    if world > 1 and not use_nccl:
-        connect_peers(dist, sim, world)
+    kw.update(device=local, rank=rank, nranks=world, nccl_unique_id=uid)
+    sim = peer_sim(eng, dist, world, **kw) if (world > 1 and not use_nccl) else eng.Sim(**kw)
     id_base = rank * n_local
     P = CFG2["poisson_steps"]
 

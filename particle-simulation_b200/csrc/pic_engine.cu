@@ -627,33 +627,40 @@ int Sim::peer_connect(const void* handles) {
     if (charge_valid) return fail("picb200_peer_connect must precede the first Poisson step", "Peer setup");
     if (nvls && !nvls_bound) {
         DrvApi* d = drv_api();
+        // a rank that cannot go on says so in the shared segment, so that the others give up at once instead of waiting
+        ShmBarrier* bar = shm_barrier_open(h0.nv.shm, false);
+        if (!bar) return fail("cannot open the shared-memory segment of the set-up barrier", "Peer setup");
+        auto give_up = [&](const std::string& what, const char* where) { shm_barrier_fail(bar); munmap(bar, 4096); return fail(what, where); };
         CUdevice dev;
-        CKD(d->cuDeviceGet_(&dev, device), "Peer setup (multicast object)");
+        CUresult r = d->cuDeviceGet_(&dev, device);
+        if (r != CUDA_SUCCESS) return give_up(drv_error(d, r) + " (cuDeviceGet)", "Peer setup (multicast object)");
+        if (const char* tf = getenv("PICB200_NVLS_TEST_FAIL"))              // tests: this rank's set-up fails (the callers' fall-back path)
+            if (tf[0] && atoi(tf) == cfg.rank) return give_up("PICB200_NVLS_TEST_FAIL", "Peer setup (multicast object)");
         if (cfg.rank != 0) {
             if (h0.pid == (long long)getpid()) {
                 nvls_mc = (CUmemGenericAllocationHandle)h0.nv.mc;          // (released by rank 0's Sim)
             } else {
                 const int fd = steal_fd(h0.pid, h0.nv.fd);
-                if (fd < 0) return fail("cannot duplicate the multicast object's file descriptor out of rank 0's process (pidfd_getfd)", "Peer setup");
-                CUresult r = d->cuMemImportFromShareableHandle_(&nvls_mc, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+                if (fd < 0) return give_up("cannot duplicate the multicast object's file descriptor out of rank 0's process (pidfd_getfd)", "Peer setup");
+                r = d->cuMemImportFromShareableHandle_(&nvls_mc, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
                 close(fd);
-                if (r != CUDA_SUCCESS) return fail(drv_error(d, r) + " (cuMemImportFromShareableHandle)", "Peer setup (multicast object)");
+                if (r != CUDA_SUCCESS) return give_up(drv_error(d, r) + " (cuMemImportFromShareableHandle)", "Peer setup (multicast object)");
                 nvls_mc_owner = true;
             }
         }
-        ShmBarrier* bar = shm_barrier_open(h0.nv.shm, false);
-        if (!bar) return fail("cannot open the shared-memory segment of the set-up barrier", "Peer setup");
-        CKD(d->cuMulticastAddDevice_(nvls_mc, dev), "Peer setup (multicast object)");
-        if (!shm_barrier_wait(bar, 0, cfg.nranks)) return fail("the ranks did not all reach picb200_peer_connect (it is collective)", "Peer setup");
-        CKD(d->cuMulticastBindMem_(nvls_mc, 0, nvls_mem, 0, nvls_bytes, 0), "Peer setup (multicast bind)");
-        CKD(d->cuMemAddressReserve_(&nvls_mv, nvls_bytes, kGridBytes, 0, 0), "Peer setup (multicast map)");
-        CKD(d->cuMemMap_(nvls_mv, nvls_bytes, 0, nvls_mc, 0), "Peer setup (multicast map)");
+        r = d->cuMulticastAddDevice_(nvls_mc, dev);
+        if (r != CUDA_SUCCESS) return give_up(drv_error(d, r) + " (cuMulticastAddDevice)", "Peer setup (multicast object)");
+        if (!shm_barrier_wait(bar, 0, cfg.nranks)) return give_up("not every rank reached picb200_peer_connect with a multicast object (the call is collective)", "Peer setup");
+        r = d->cuMulticastBindMem_(nvls_mc, 0, nvls_mem, 0, nvls_bytes, 0);
+        if (r == CUDA_SUCCESS) r = d->cuMemAddressReserve_(&nvls_mv, nvls_bytes, kGridBytes, 0, 0);
+        if (r == CUDA_SUCCESS) r = d->cuMemMap_(nvls_mv, nvls_bytes, 0, nvls_mc, 0);
         CUmemAccessDesc ad;
         ad.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
         ad.location.id = device;
         ad.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
-        CKD(d->cuMemSetAccess_(nvls_mv, nvls_bytes, &ad, 1), "Peer setup (multicast map)");
-        if (!shm_barrier_wait(bar, 1, cfg.nranks)) return fail("the ranks did not all bind their grids", "Peer setup");
+        if (r == CUDA_SUCCESS) r = d->cuMemSetAccess_(nvls_mv, nvls_bytes, &ad, 1);
+        if (r != CUDA_SUCCESS) return give_up(drv_error(d, r) + " (binding / mapping the multicast object)", "Peer setup (multicast bind)");
+        if (!shm_barrier_wait(bar, 1, cfg.nranks)) return give_up("not every rank bound its grids to the multicast object", "Peer setup");
         munmap(bar, 4096);
         if (cfg.rank == 0) {
             shm_unlink(nvls_shm); nvls_shm[0] = 0;

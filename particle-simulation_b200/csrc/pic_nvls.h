@@ -98,14 +98,17 @@ inline ShmBarrier* shm_barrier_open(const char* name, bool create) {
     close(fd);
     return p == MAP_FAILED ? nullptr : static_cast<ShmBarrier*>(p);      // (a fresh segment is all zero)
 }
+// count[3]: ranks whose set-up failed -- nobody waits for them (they say so and everybody gives up at once)
+inline void shm_barrier_fail(ShmBarrier* b) { b->count[3].fetch_add(1, std::memory_order_acq_rel); }
 inline bool shm_barrier_wait(ShmBarrier* b, int which, int nranks, int timeout_s = 60) {
     b->count[which].fetch_add(1, std::memory_order_acq_rel);
     const auto t0 = std::chrono::steady_clock::now();
     while (b->count[which].load(std::memory_order_acquire) < nranks) {
+        if (b->count[3].load(std::memory_order_acquire) > 0) return false;
         if (std::chrono::steady_clock::now() - t0 > std::chrono::seconds(timeout_s)) return false;
         std::this_thread::sleep_for(std::chrono::microseconds(50));
     }
-    return true;
+    return b->count[3].load(std::memory_order_acquire) == 0;
 }
 
 // a file descriptor of another process of this user, duplicated into this one (Linux >= 5.6)
