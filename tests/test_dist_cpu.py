@@ -23,3 +23,15 @@ def test_reference_arm_only_rank0_prints():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
                        capture_output=True, text=True, timeout=120, env=env, cwd=ROOT)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_setup_barrier_between_processes(tmp_path):
+    """csrc/pic_nvls.h without a GPU: the shared-memory barrier of picb200_peer_connect between forked processes (eight
+    ranks meet twice; a rank that reports a failure makes the others give up within a second; an absent rank costs the
+    time-out), and a file descriptor duplicated out of another process (pidfd_getfd), as the multicast object's is."""
+    exe = tmp_path / "csb"
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    inc = "/usr/local/cuda/include"
+    subprocess.run([cxx, "-O1", "-std=c++17", "-I", inc, "-o", str(exe), os.path.join(ROOT, "tests", "tools", "check_shm_barrier.cpp"), "-lpthread"], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.startswith("ok"), r.stdout + r.stderr

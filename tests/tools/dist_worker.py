@@ -31,6 +31,39 @@ assert [h[0] for h in handles] == list(range(world)) and all(len(h) == eng.PEER_
 assert bench.all_max(dist, float(rank + 1)) == float(world)
 assert bench.all_sum(dist, float(rank + 1)) == world * (world + 1) / 2
 
+# bench.peer_sim: the multicast set-up of the in-kernel exchange fails on ONE rank (here: a stand-in engine whose rank 1
+# cannot connect while PICB200_NVLS is on) -> the ranks agree over gloo and ALL fall back to the unicast exchange
+class FakeErr(RuntimeError):
+    pass
+
+
+class FakeSim:
+    made = 0
+
+    def __init__(self, **kw):
+        FakeSim.made += 1
+        self.nvls = os.environ.get("PICB200_NVLS", "1") != "0"
+        self.closed = False
+
+    def peer_export(self):
+        return bytes([rank]) * eng.PEER_HANDLE_BYTES
+
+    def peer_connect(self, hs):
+        assert [h[0] for h in hs] == list(range(world))
+        if self.nvls and rank == 1:
+            raise FakeErr("CUDA error: multicast set-up failed\nAt: Peer setup")
+
+    def close(self):
+        self.closed = True
+
+
+import types  # noqa: E402
+os.environ.pop("PICB200_NVLS", None)
+sim = bench.peer_sim(types.SimpleNamespace(Sim=FakeSim, EngineError=FakeErr), dist, world)
+assert FakeSim.made == 2 and not sim.nvls and not sim.closed and os.environ["PICB200_NVLS"] == "0"
+assert "fell back" in bench.PEER_TRANSPORT["note"] and "PICB200_NVLS=0" in bench.PEER_TRANSPORT["kind"]
+os.environ.pop("PICB200_NVLS", None)
+
 # no GPU here: a rank must fail loudly, never fall back to a CPU path
 no_gpu = eng.device_count() == 0
 if no_gpu:
