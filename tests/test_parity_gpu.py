@@ -454,6 +454,32 @@ def test_streaming_step_loop_matches_oracle(engine, oracle, monkeypatch, stream_
     assert ((e ** 2).sum(axis=0) > 5.7).sum() > 1000           # rows beyond the window were in use until the end
 
 
+@pytest.mark.parametrize("pt", [3, 10])
+def test_uploaded_timestamps_first_launch_generic(engine, oracle, pt):
+    """A population uploaded WITH timestamps (some electrons "born at step t" of the coming Poisson step, src/pic.cu:218:
+    their first push is step t + 1): the fused kernel's generic chunk path.  The streaming instantiation (poisson_timestep
+    <= 3) has no copy of that path; the host runs the first launch after such an upload on the plain instantiation, which
+    leaves every timestamp at -1, and streams from the second launch on.  Same bits as the oracle after each launch."""
+    rows = np.tile(np.array([[2.0, 1.0]], dtype=np.float32), (10000, 1))
+    rng = np.random.default_rng(41)
+    n = 50001
+    pos = rng.uniform(2.45, 2.7, size=(3, n)).astype(np.float32)
+    vel = (rng.normal(size=(3, n)) * 0.05).astype(np.float32)
+    ts = np.full(n, -1, dtype=np.int32)
+    ts[::3] = rng.integers(1, pt, size=len(ts[::3]))            # a third arrives "born" somewhere inside the step
+    with engine.Sim(capacity=8 * n, poisson_timestep=pt, mode=0, table_rows=rows, poisson_steps=6) as sim:
+        sim.upload(*pos, *vel, ts=ts)
+        o = oracle.Oracle(capacity=8 * n, poisson_timestep=pt, table_rows=rows, threads=4)
+        o.upload(*pos, *vel, ts=ts)
+        for k in (1, 2, 3):
+            sim.run_steps(k)
+            o.run(k)
+            m, c = sim.summary(), o.counters()
+            assert (m["final_n"], m["total_added"], m["total_removed"], m["pushes"]) == (c["n"], c["added"], c["removed"], c["pushes"]), k
+            assert_state_equal(sim.download(), o.download_sorted())
+    assert c["added"] > 100 and c["pushes"] < 6 * pt * 2 * n
+
+
 def test_lazy_compaction_parks_children_near_capacity(engine, oracle):
     """Holes in place shift the slots of new children upwards; a child whose shifted slot passes the capacity
     while the reference's counter does not is parked and placed by the compaction the step then ends with.
