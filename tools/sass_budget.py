@@ -33,7 +33,7 @@ def source_sections():
     f0 = find(mv, "__device__ __forceinline__ void lockstep_push(")
     loop = find(mv, "for (int t = t_first; t <= c.pt; ++t)", f0)
     sec = {}
-    sec["philox"] = [(MOVER, find(mv, "if (t == t_first || (g & 3u) == 0u", loop), find(mv, "refresh = false;", loop) + 1),
+    sec["philox"] = [(MOVER, find(mv, "if ((t != t_first && (g & 3u) == 0u)", loop), find(mv, "refresh = false;", loop) + 1),
                      (DEVICE, find(dv, "uint4 philox4x32_10("), find(dv, "return c;", find(dv, "uint4 philox4x32_10(uint4 c, const PhiloxKeys& ks)")))]
     sec["leapfrog"] = [(MOVER, find(mv, "const bool act = kStaged", loop), find(mv, "if (!kStaged || act)", loop))]
     sec["bounds"] = [(MOVER, find(mv, "const bool oob =", loop), find(mv, "const bool oob =", loop))]
