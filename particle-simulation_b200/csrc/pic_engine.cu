@@ -422,6 +422,7 @@ int Sim::create(const picb200_config* c) {
     if (field_ratio >= 0 && ((cfg.nranks == 1 && (fused || field_launch)) || (cfg.nranks > 1 && fused && !cfg.nccl_unique_id)))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
         CK(cudaMalloc(&field, (size_t)kGrid * kGrid * kGrid * sizeof(float4)), "Grid alloc");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
+    CK(cudaFuncSetAttribute(k_mover<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
 
     if (cfg.nranks > 1) {
         if (cfg.nranks > kMaxRanks) return fail("at most 8 ranks", "picb200_create");
@@ -803,7 +804,8 @@ int Sim::launch_mover_window(int lo, int hi, int t_from, int t_to, bool stepwise
     // hi < 0: the window ends at DevState::win_hi, which the host does not know: a full grid, grid-stride loop
     const int blocks = hi < 0 ? sm_count : std::max(1, std::min(sm_count, (hi - lo + mover_threads - 1) / mover_threads));
     span_begin(kPhMover);
-    k_mover<false><<<blocks, mover_threads, kMoverSmemBytes(mover_threads), stream>>>(a);
+    if (stepwise) k_mover<false, true><<<blocks, mover_threads, kMoverSmemBytes(mover_threads), stream>>>(a);
+    else k_mover<false><<<blocks, mover_threads, kMoverSmemBytes(mover_threads), stream>>>(a);
     ++launches; ++mover_launches;
     span_end();
     CK_LAST("Mobility steps");

@@ -211,13 +211,10 @@ __device__ __forceinline__ void advance(const MoverCtx& c, El& e, bool& alive, i
 
 // One 32-electron chunk straight from the global store: slots [i0, i0+32) clipped to `end`.
 // kLaterGen: fall-back pass of the persistent kernel -- only spilled children (ts >= 0) need work.
-template <bool kCountSpill, bool kLaterGen>
-__device__ __forceinline__ void process_chunk(const MoverCtx& c, int i0, int end, int t_from, int t_to, int& staged,
-                                              unsigned& pushes, int& dead) {
-    const int i = i0 + c.lane;
-    const bool in = i < end;
-    El e{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    int ts = kDead;
+// In two halves, so that the windowed launches of modes 31/32 can have the NEXT chunk's loads in flight while they push.
+__device__ __forceinline__ void chunk_load(const MoverCtx& c, int i, bool in, El& e, int& ts) {
+    e = El{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    ts = kDead;
     if (in) {
         e.x = __ldcg(c.s.x + i); e.y = __ldcg(c.s.y + i); e.z = __ldcg(c.s.z + i);
         e.vx = __ldcg(c.s.vx + i); e.vy = __ldcg(c.s.vy + i); e.vz = __ldcg(c.s.vz + i);
@@ -225,12 +222,16 @@ __device__ __forceinline__ void process_chunk(const MoverCtx& c, int i0, int end
         ts = __ldcg(c.s.ts + i);
         e.id = __ldcg(c.s.id + i);
     }
+}
+template <bool kCountSpill, bool kLaterGen, int kSmemRows = kRows>
+__device__ __forceinline__ void chunk_push_store(const MoverCtx& c, int i, bool in, El& e, int ts, int t_from, int t_to, int& staged,
+                                                 unsigned& pushes, int& dead) {
     const bool was_alive = in && (kLaterGen ? ts >= 0 : ts != kDead);
     bool alive = was_alive;
     // first step of this electron: max(1, timestamp+1)  (src/pic.cu:218)
     const int t0 = max(t_from, max(1, ts + 1));
     bool touched = false;
-    advance<kCountSpill>(c, e, alive, t0, t_to, staged, pushes, dead, touched);
+    advance<kCountSpill, kSmemRows>(c, e, alive, t0, t_to, staged, pushes, dead, touched);
     if (was_alive) {
         if (touched) {
             __stcg(c.s.x + i, e.x); __stcg(c.s.y + i, e.y); __stcg(c.s.z + i, e.z);
@@ -241,6 +242,16 @@ __device__ __forceinline__ void process_chunk(const MoverCtx& c, int i0, int end
         const int ts1 = !alive ? kDead : (t_to == c.pt ? -1 : ts);
         if (ts1 != ts) __stcg(c.s.ts + i, ts1);
     }
+}
+template <bool kCountSpill, bool kLaterGen>
+__device__ __forceinline__ void process_chunk(const MoverCtx& c, int i0, int end, int t_from, int t_to, int& staged,
+                                              unsigned& pushes, int& dead) {
+    const int i = i0 + c.lane;
+    const bool in = i < end;
+    El e;
+    int ts;
+    chunk_load(c, i, in, e, ts);
+    chunk_push_store<kCountSpill, kLaterGen>(c, i, in, e, ts, t_from, t_to, staged, pushes, dead);
 }
 
 // Persistent kernel only: the warp takes the children waiting in its own stage into registers,
@@ -301,7 +312,7 @@ __device__ __forceinline__ int mover_barrier_next_window(DevState* st, unsigned 
     return s_hi;
 }
 
-template <bool kPersistent>
+template <bool kPersistent, bool kStepwise = false>
 __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     // hi < 0 / lo < 0: the window was frozen on the device by k_freeze_window (modes 31/32 without a host read per
@@ -309,12 +320,6 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     const int w_hi = (!kPersistent && a.hi < 0) ? ld_volatile_i32(&a.st->win_hi) : a.hi;
     const int w_lo = (!kPersistent && a.lo < 0) ? ld_volatile_i32(&a.st->win_lo) : a.lo;
     if (!kPersistent && w_hi <= w_lo) return;
-    {   // stage the collision tables (120 KB) once per CTA, 128-bit copies
-        const float4* src = reinterpret_cast<const float4*>(a.tables);
-        float4* dst = reinterpret_cast<float4*>(smem_raw);
-        for (int k = threadIdx.x; k < kTableSmemBytes / 16; k += blockDim.x) dst[k] = __ldg(src + k);
-    }
-    __syncthreads();
 
     MoverCtx c;
     c.s = a.s;
@@ -330,8 +335,35 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     c.stage_cap = 32;
     c.stepwise = a.stepwise;
     c.pool = nullptr;
-    c.g0 = (unsigned)a.st->poisson_index * (unsigned)a.pt;
     c.seed = a.seed;
+
+    // kStepwise -- one launch per mobility step (mode 32; the tables are staged anew by every launch): the first chunk's loads go out
+    // before the tables are staged, and only the first kStreamRows rows are -- the rest is read from the global image, as
+    // in the streaming instantiation of the fused kernel
+    constexpr bool stepwise = !kPersistent && kStepwise;      // (its own instantiation: the other two keep their code)
+    const int span = kPersistent ? 0 : w_hi - w_lo;
+    const int rounded = (span + 31) & ~31;
+    const int stride = (int)(gridDim.x * blockDim.x);
+    int k = (int)((blockIdx.x * blockDim.x + threadIdx.x) & ~31u);
+    El e0{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int ts0 = kDead;
+    bool in0 = false;
+    if (stepwise && k < rounded) {
+        in0 = w_lo + k + c.lane < w_hi;
+        chunk_load(c, w_lo + k + c.lane, in0, e0, ts0);
+    }
+    if (!stepwise) {   // stage the collision tables (120 KB) once per CTA, 128-bit copies
+        const float4* src = reinterpret_cast<const float4*>(a.tables);
+        float4* dst = reinterpret_cast<float4*>(smem_raw);
+        for (int q = threadIdx.x; q < kTableSmemBytes / 16; q += blockDim.x) dst[q] = __ldg(src + q);
+    } else {
+        const unsigned char* g = reinterpret_cast<const unsigned char*>(a.tables);
+        for (int q = threadIdx.x; q < kStreamRows * 8 / 16; q += blockDim.x) reinterpret_cast<float4*>(smem_raw)[q] = __ldg(reinterpret_cast<const float4*>(g) + q);
+        for (int q = threadIdx.x; q < kStreamRows * 4 / 16; q += blockDim.x)
+            reinterpret_cast<float4*>(smem_raw + kThrBytes)[q] = __ldg(reinterpret_cast<const float4*>(g + kThrBytes) + q);
+    }
+    __syncthreads();
+    c.g0 = (unsigned)a.st->poisson_index * (unsigned)a.pt;
 
     int staged = 0;            // warp-uniform: children waiting in this warp's stage
     unsigned pushes = 0;
@@ -363,10 +395,23 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
             lo = hi;
         }
     } else {
-        const int span = w_hi - w_lo;
-        const int rounded = (span + 31) & ~31;
-        for (int k = (blockIdx.x * blockDim.x + threadIdx.x) & ~31; k < rounded; k += gridDim.x * blockDim.x)
-            process_chunk<false, false>(c, w_lo + k, w_hi, a.t_from, a.t_to, staged, pushes, dead);
+        if (stepwise) {          // the next chunk's loads fly while this one is pushed
+            while (k < rounded) {
+                const int kn = k + stride;
+                El e1{0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+                int ts1 = kDead;
+                bool in1 = false;
+                if (kn < rounded) {
+                    in1 = w_lo + kn + c.lane < w_hi;
+                    chunk_load(c, w_lo + kn + c.lane, in1, e1, ts1);
+                }
+                chunk_push_store<false, false, kStreamRows>(c, w_lo + k + c.lane, in0, e0, ts0, a.t_from, a.t_to, staged, pushes, dead);
+                e0 = e1; ts0 = ts1; in0 = in1; k = kn;
+            }
+        } else {                 // a window through all its mobility steps (mode 31): slower with either (twelve more live
+                                 // registers through ten steps, a window test in every step)
+            for (; k < rounded; k += stride) process_chunk<false, false>(c, w_lo + k, w_hi, a.t_from, a.t_to, staged, pushes, dead);
+        }
         if (staged) { stage_spill<false>(c, staged); staged = 0; }
     }
 
