@@ -415,10 +415,12 @@ int Sim::create(const picb200_config* c) {
     if (const char* fr = getenv("PICB200_FIELD_RATIO")) field_ratio = atoi(fr);
     // several ranks: the pass over the union box and its grid barrier are paid per rank whatever the slab holds: large slabs only
     field_min_n = getenv("PICB200_FIELD_MIN_N") ? atoi(getenv("PICB200_FIELD_MIN_N")) : (cfg.nranks > 1 ? 3000000 : 0);
-    // modes 31/32: the per-cell field is one more launch per Poisson step (18 us measured, whether it finds a dense plasma or
-    // not), which pays from about 2e6 electrons; the step's graph is captured once, so the configured population decides
+    // modes 31/32: the per-cell field is one more launch per Poisson step (2 % of a step when it finds a sparse plasma and
+    // returns); the six-point gather is bound by the L1's tag stage, one sector per cycle and SM (1e6 electrons: 29 us,
+    // against 11 us for field + one sector per electron).  The step's graph is captured once, so the configured population
+    // decides: from 5e5 electrons, which the initial 62^3-cell cube holds at 2 per cell (the device's own density rule)
     field_launch = !fused && field_ratio >= 0 && cfg.nranks == 1 &&
-                   (getenv("PICB200_FIELD_LAUNCH") ? atoi(getenv("PICB200_FIELD_LAUNCH")) != 0 : cfg.init_n >= 2000000);
+                   (getenv("PICB200_FIELD_LAUNCH") ? atoi(getenv("PICB200_FIELD_LAUNCH")) != 0 : cfg.init_n >= 500000);
     if (field_ratio >= 0 && ((cfg.nranks == 1 && (fused || field_launch)) || (cfg.nranks > 1 && fused && !cfg.nccl_unique_id)))      // 16-byte field records over the dense grid; only cells of the occupied box are ever written or read
         CK(cudaMalloc(&field, (size_t)kGrid * kGrid * kGrid * sizeof(float4)), "Grid alloc");
     CK(cudaFuncSetAttribute(k_mover<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMoverSmemBytes(1024)), "Mover attr");
@@ -477,9 +479,10 @@ int Sim::warm_kernels() {
             if (launch_fused(a, false, variants[k])) return 1;
         }
     }
+    if (step_graph) CK(cudaGraphLaunch(step_graph, stream), "Warm-up");     // modes 31/32: one Poisson step over the empty population
     CK(cudaStreamSynchronize(stream), "Warm-up");
     CK_LAST("Warm-up");
-    return reset_state();                                                   // (k_mobility_begin touched the counters)
+    return reset_state();                                                   // (the counters were touched)
 }
 
 // What one rank tells the others (picb200_peer_export -> picb200_peer_connect): where its two local
@@ -743,7 +746,8 @@ int Sim::op_gather() {
     // dense plasma (decided on the device): the field once per cell of the occupied box, then one record per electron
     float4* const F = (cfg.nranks == 1 && field_launch) ? field : nullptr;
     if (F) { k_field_box<<<aux_blocks, 256, 0, stream>>>(st, grid[cur], F, efc, cur, field_ratio); ++launches; }
-    k_gather<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, F, cur, field_ratio);
+    if (F) k_gather<true><<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, F, cur, field_ratio);
+    else k_gather<false><<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, nullptr, cur, field_ratio);
     ++launches;
     span_end();
     CK_LAST("Gather");

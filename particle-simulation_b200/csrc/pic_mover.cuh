@@ -317,8 +317,8 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     // hi < 0 / lo < 0: the window was frozen on the device by k_freeze_window (modes 31/32 without a host read per
     // launch); an empty one ends the launch before anything is staged
-    const int w_hi = (!kPersistent && a.hi < 0) ? ld_volatile_i32(&a.st->win_hi) : a.hi;
-    const int w_lo = (!kPersistent && a.lo < 0) ? ld_volatile_i32(&a.st->win_lo) : a.lo;
+    const int w_hi = (!kPersistent && a.hi < 0) ? ld_state_i32(&a.st->win_hi) : a.hi;
+    const int w_lo = (!kPersistent && a.lo < 0) ? ld_state_i32(&a.st->win_lo) : a.lo;
     if (!kPersistent && w_hi <= w_lo) return;
 
     MoverCtx c;
@@ -362,8 +362,9 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
         for (int q = threadIdx.x; q < kStreamRows * 4 / 16; q += blockDim.x)
             reinterpret_cast<float4*>(smem_raw + kThrBytes)[q] = __ldg(reinterpret_cast<const float4*>(g + kThrBytes) + q);
     }
+    const unsigned pidx = (unsigned)a.st->poisson_index;
     __syncthreads();
-    c.g0 = (unsigned)a.st->poisson_index * (unsigned)a.pt;
+    c.g0 = pidx * (unsigned)a.pt;
 
     int staged = 0;            // warp-uniform: children waiting in this warp's stage
     unsigned pushes = 0;
@@ -419,6 +420,22 @@ __global__ void __launch_bounds__(1024, 1) k_mover(MoverArgs a) {
     for (int o = 16; o > 0; o >>= 1) {
         pushes += __shfl_down_sync(kFull, pushes, o);
         dead += __shfl_down_sync(kFull, dead, o);
+    }
+    if (!kPersistent) {          // 4736 warps and two counters: one atomic per BLOCK (the launches of a small population are short)
+        __shared__ unsigned s_pushes;
+        __shared__ int s_dead;
+        if (threadIdx.x == 0) { s_pushes = 0; s_dead = 0; }
+        __syncthreads();
+        if (c.lane == 0) {
+            if (pushes) atomicAdd(&s_pushes, pushes);
+            if (dead) atomicAdd(&s_dead, dead);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (s_pushes) atomicAdd(&a.st->pushes, (unsigned long long)s_pushes);
+            if (s_dead) atomicAdd(&a.st->n_dead, s_dead);
+        }
+        return;
     }
     if (c.lane == 0) {
         if (pushes) atomicAdd(&a.st->pushes, (unsigned long long)pushes);
@@ -666,9 +683,9 @@ __device__ __forceinline__ void gather_field(const FusedCtx& f, int ix, int iy, 
 constexpr int kGridPhaseUnroll = 4;
 // dense plasma, decided on the device from words every block reads alike: the box of grid `which` and n
 __device__ __forceinline__ bool box_is_dense(const DevState* st, int which, int ratio, int* box /* out: lo xyz, hi xyz */) {
-    for (int k = 0; k < 3; ++k) { box[k] = ld_volatile_i32(&st->bbox_lo[which][k]); box[3 + k] = ld_volatile_i32(&st->bbox_hi[which][k]); }
+    for (int k = 0; k < 3; ++k) { box[k] = ld_state_i32(&st->bbox_lo[which][k]); box[3 + k] = ld_state_i32(&st->bbox_hi[which][k]); }
     const long long cells = (long long)max(0, box[3] - box[0] + 1) * max(0, box[4] - box[1] + 1) * max(0, box[5] - box[2] + 1);
-    return ratio >= 0 && cells > 0 && (long long)ld_volatile_i32(&st->n) >= (long long)ratio * cells;
+    return ratio >= 0 && cells > 0 && (long long)ld_state_i32(&st->n) >= (long long)ratio * cells;
 }
 __device__ __forceinline__ void stage_cell_bounds(float* s_bnd, const float* __restrict__ g_bnd) {
     for (int k = threadIdx.x; k <= kGrid; k += blockDim.x) s_bnd[k] = __ldg(g_bnd + k);
@@ -734,6 +751,9 @@ __global__ void k_field_box(const DevState* st, const int* __restrict__ charge, 
 // K_gather: gridToParticles (src/grid_operations.cu:59-72) from the per-cell field of k_field_box, or -- sparse plasma --
 // updateGrid + gridToParticles for the electron's own cell: the six neighbour counts differenced on the spot,
 // acc = float(EFC * double(c+ - c-)), absent neighbours at the domain faces count 0.  Same expression, same bits.
+// kField: launched with a per-cell field (the host expects a dense plasma; the device decides); without one the six-point
+// gather runs with all its loads up front, which costs registers the other instantiation needs for its occupancy.
+template <bool kField>
 __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ charge, double efc, const float* __restrict__ g_bnd,
                          const float4* __restrict__ F, int which, int ratio) {
     __shared__ float s_bnd[kGrid + 1];
@@ -741,7 +761,7 @@ __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ char
     if ((int)(blockIdx.x * blockDim.x) >= n) return;
     stage_cell_bounds(s_bnd, g_bnd);
     int box[6];
-    const bool dense = F != nullptr && box_is_dense(st, which, ratio, box);
+    const bool dense = kField && F != nullptr && box_is_dense(st, which, ratio, box);
     const int stride = gridDim.x * blockDim.x;
     for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += kGridPhaseUnroll * stride) {
         float px[kGridPhaseUnroll], py[kGridPhaseUnroll], pz[kGridPhaseUnroll];
@@ -760,7 +780,7 @@ __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ char
                 const int i = i0 + u * stride;
                 if (i < n) { __stcg(s.ax + i, v[u].x); __stcg(s.ay + i, v[u].y); __stcg(s.az + i, v[u].z); }
             }
-        } else {
+        } else if (kField) {
 #pragma unroll
             for (int u = 0; u < kGridPhaseUnroll; ++u) {
                 const int i = i0 + u * stride;
@@ -768,6 +788,31 @@ __global__ void k_gather(Soa s, const DevState* st, const int* __restrict__ char
                     float ax, ay, az;
                     gather_field_direct(charge, efc, cell_of_fast(px[u], s_bnd), cell_of_fast(py[u], s_bnd), cell_of_fast(pz[u], s_bnd), ax, ay, az);
                     __stcg(s.ax + i, ax); __stcg(s.ay + i, ay); __stcg(s.az + i, az);
+                }
+            }
+        } else {
+            // all 24 neighbour counts first, then the differences and the stores: taken one electron at a time the stores'
+            // memory clobber keeps the next electron's loads behind them -- four L2 round trips in a row per thread
+            int d[kGridPhaseUnroll][3];
+#pragma unroll
+            for (int u = 0; u < kGridPhaseUnroll; ++u) {
+                d[u][0] = d[u][1] = d[u][2] = 0;
+                if (i0 + u * stride < n) {
+                    const int ix = cell_of_fast(px[u], s_bnd), iy = cell_of_fast(py[u], s_bnd), iz = cell_of_fast(pz[u], s_bnd);
+                    const int* q = charge + cell_index(ix, iy, iz);
+                    const int xm = (ix != 0) ? __ldcg(q - 1) : 0, xp = (ix != kGrid - 1) ? __ldcg(q + 1) : 0;
+                    const int ym = (iy != 0) ? __ldcg(q - kGrid) : 0, yp = (iy != kGrid - 1) ? __ldcg(q + kGrid) : 0;
+                    const int zm = (iz != 0) ? __ldcg(q - kGrid * kGrid) : 0, zp = (iz != kGrid - 1) ? __ldcg(q + kGrid * kGrid) : 0;
+                    d[u][0] = xp - xm; d[u][1] = yp - ym; d[u][2] = zp - zm;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kGridPhaseUnroll; ++u) {
+                const int i = i0 + u * stride;
+                if (i < n) {                                     // the expression of gather_field_direct
+                    __stcg(s.ax + i, __double2float_rn(__dmul_rn(efc, (double)d[u][0])));
+                    __stcg(s.ay + i, __double2float_rn(__dmul_rn(efc, (double)d[u][1])));
+                    __stcg(s.az + i, __double2float_rn(__dmul_rn(efc, (double)d[u][2])));
                 }
             }
         }
