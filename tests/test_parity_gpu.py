@@ -390,7 +390,7 @@ def test_per_cell_field_path_matches_oracle(engine, oracle, monkeypatch, ratio, 
     differencing six counts per electron.  PICB200_FIELD_RATIO (read at create) moves the density from which it
     does: -1 never, 0 always, 1 and 16 electrons per cell (the population below has ~3).  Same bits.
     Modes 31/32 (mode 1, 2 here) do the same with a kernel of their own (k_field_box) in front of the gather; it is
-    part of their grid phase from 2e6 configured electrons, PICB200_FIELD_LAUNCH=1 puts it there for this small one."""
+    part of their grid phase from 5e5 configured electrons, PICB200_FIELD_LAUNCH=1 puts it there for this small one."""
     monkeypatch.setenv("PICB200_FIELD_LAUNCH", "1")
     rows = np.tile(np.array([[3.0, 1.0]], dtype=np.float32), (10000, 1))
     rng = np.random.default_rng(77)
