@@ -405,9 +405,13 @@ __global__ void k_freeze_window(DevState* st, int capacity, int advance) {
     if (advance) st->win_lo = st->win_hi;
     st->win_hi = min(st->n_alloc, capacity);
 }
-__global__ void k_mobility_begin(DevState* st) {
+// The window of the first launch is [0, min(n, capacity)) in modes 31 and 32 alike, so no k_freeze_window precedes it;
+// reset_box >= 0: also k_reset_bbox for that grid (one single-thread launch instead of three per Poisson step).
+__global__ void k_mobility_begin(DevState* st, int capacity, int reset_box) {
+    if (reset_box >= 0)
+        for (int k = 0; k < 3; ++k) { st->bbox_lo[reset_box][k] = kGrid; st->bbox_hi[reset_box][k] = -1; }
     st->n_alloc = st->n;
-    st->win_lo = 0; st->win_hi = 0;
+    st->win_lo = 0; st->win_hi = min(st->n, capacity);
     st->top_alloc = st->n;
     st->n_dead = 0;
     st->n_holes = 0; st->n_movers = 0;

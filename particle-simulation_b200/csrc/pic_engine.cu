@@ -208,8 +208,8 @@ struct Sim {
     int init_uniform(int init_n, unsigned long long id_base);
     int op_deposit();
     int op_gather();
-    int op_clear();
-    int op_mobility_begin();
+    int op_clear(bool reset_box = true);
+    int op_mobility_begin(int reset_box = -1);
     int op_mobility();
     int op_compact();
     int op_step_end();
@@ -469,7 +469,7 @@ int Sim::warm_kernels() {
     if (getenv("PICB200_NO_WARM")) return 0;
     k_clear_box<<<1, 32, 0, stream>>>(st, grid[2], 2);                      // (all boxes are empty)
     k_deposit<<<1, 256, 0, stream>>>(soa, st, grid[0], 0, tables + kTableSmemBytes / 4);    // n == 0
-    k_mobility_begin<<<1, 1, 0, stream>>>(st);
+    k_mobility_begin<<<1, 1, 0, stream>>>(st, cfg.capacity, -1);
     if (fused && cfg.nranks == 1) {
         const bool adopt = cfg.poisson_timestep >= (getenv("PICB200_ADOPT_STEPS") ? atoi(getenv("PICB200_ADOPT_STEPS")) : kAdoptMinSteps);
         const bool streaming = !adopt && mover_threads == 1024 && cfg.poisson_timestep <= (getenv("PICB200_STREAM_STEPS") ? atoi(getenv("PICB200_STREAM_STEPS")) : kStreamMaxSteps);
@@ -753,12 +753,12 @@ int Sim::op_gather() {
     CK_LAST("Gather");
     return 0;
 }
-int Sim::op_clear() {
+int Sim::op_clear(bool reset_box) {       // reset_box false: the caller's op_mobility_begin(cur) resets the box
     span_begin(kPhClear);
     k_clear_box<<<aux_blocks, 256, 0, stream>>>(st, grid[cur], cur);
-    k_reset_bbox<<<1, 32, 0, stream>>>(st, cur);
+    if (reset_box) k_reset_bbox<<<1, 32, 0, stream>>>(st, cur);
     charge_valid = false;
-    launches += 2;
+    launches += reset_box ? 2 : 1;
     span_end();
     CK_LAST("Clear grid");
     return 0;
@@ -795,8 +795,8 @@ int Sim::allreduce_charge() {
 }
 
 // ---- mobility phase (src/pic.cu:509-537) -----------------------------------------------------
-int Sim::op_mobility_begin() {
-    k_mobility_begin<<<1, 1, 0, stream>>>(st);
+int Sim::op_mobility_begin(int reset_box) {
+    k_mobility_begin<<<1, 1, 0, stream>>>(st, cfg.capacity, reset_box);
     ++launches;
     CK_LAST("Mobility steps");
     return 0;
@@ -836,8 +836,7 @@ int Sim::op_mobility() {
                 // a child of generation g is born at step g or later: poisson_timestep + 1 passes always suffice, and
                 // the passes that find no children return at once.  No host read, the step can be replayed as a graph.
                 for (int g = 0; g <= pt; ++g) {
-                    k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity, 1);
-                    ++launches;
+                    if (g) { k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity, 1); ++launches; }     // (the first window: k_mobility_begin)
                     if (launch_mover_window(-1, -1, 1, pt, false)) return 1;
                 }
                 break;
@@ -856,8 +855,7 @@ int Sim::op_mobility() {
             // The reference copies n to the host before every launch; here the window of a step is frozen on the
             // device (k_freeze_window) and the host only looks when a logger wants the state.
             for (int t = 1; t <= pt; ++t) {
-                k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity, 0);
-                ++launches;
+                if (t > 1) { k_freeze_window<<<1, 1, 0, stream>>>(st, cfg.capacity, 0); ++launches; }      // (the first window: k_mobility_begin)
                 if (launch_mover_window(0, -1, t, t, true)) return 1;
                 if (naive_hook) {
                     if (sync_state()) return 1;
@@ -970,7 +968,7 @@ int Sim::poisson_step(bool sync) {
         charge_valid = true;
         return sync ? sync_state() : 0;
     }
-    if (op_deposit() || op_gather() || op_clear() || op_mobility_begin() || op_mobility() || op_compact() || op_step_end()) return 1;
+    if (op_deposit() || op_gather() || op_clear(false) || op_mobility_begin(cur) || op_mobility() || op_compact() || op_step_end()) return 1;
     if (sync) return sync_state();
     return 0;
 }
@@ -983,7 +981,7 @@ int Sim::build_step_graph() {
     const bool cv = charge_valid;
     cudaGraph_t captured = nullptr;
     CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal), "Graph capture");
-    const int rc = op_deposit() || op_gather() || op_clear() || op_mobility_begin() || op_mobility() || op_compact() || op_step_end();
+    const int rc = op_deposit() || op_gather() || op_clear(false) || op_mobility_begin(cur) || op_mobility() || op_compact() || op_step_end();
     const cudaError_t e = cudaStreamEndCapture(stream, &captured);
     graph_launches = launches - l0; graph_mover_launches = mover_launches - m0;
     launches = l0; mover_launches = m0; charge_valid = cv;
