@@ -125,6 +125,8 @@ struct Sim {
     int fused_smem_pad = 0;          // PICB200_SMEM_PAD: extra dynamic shared memory for the fused kernel (carve-out experiments)
     int blocks_per_sm = 1;
     int aux_blocks = 0;
+    int gather_blocks[2] = {0, 0};   // grid of k_gather<false/true>, sized by the configured population
+    int deposit_blocks = 0;          // grid of k_deposit, likewise
     uint2 seed{};
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
@@ -315,6 +317,16 @@ int Sim::create(const picb200_config* c) {
     mover_threads = bs * blocks_per_sm;
     if (const char* mt = getenv("PICB200_MOVER_THREADS")) mover_threads = std::max(32, std::min(1024, (atoi(mt) / 32) * 32));   // (experiments: how the fused kernel's rate depends on the warps per SM)
     aux_blocks = sm_count * 8;
+    // k_gather is latency-bound and likes few trips per thread (1e7 electrons: 8 blocks per SM 3.62 ms, 32: 3.26, 64: 3.19 for
+    // cfg5 mode 32 at poisson_timestep = 1; 1e6 electrons: 8 is best by 1 %): one trip of four electrons per thread for the
+    // configured population, within [8, 64] blocks per SM (the step's graph is captured once)
+    {
+        const long long want = ((long long)cfg.init_n + 1024LL * sm_count - 1) / (1024LL * sm_count);
+        const int per_sm = getenv("PICB200_GATHER_BLOCKS") ? std::max(1, atoi(getenv("PICB200_GATHER_BLOCKS"))) : (int)std::max(8LL, std::min(64LL, want));
+        gather_blocks[0] = gather_blocks[1] = sm_count * per_sm;
+        // k_deposit likewise, up to 32 per SM (every block ends with six atomics on the box words): 3.18 -> 3.11 ms there
+        deposit_blocks = sm_count * (getenv("PICB200_DEPOSIT_BLOCKS") ? std::max(1, atoi(getenv("PICB200_DEPOSIT_BLOCKS"))) : (int)std::max(8LL, std::min(32LL, want)));
+    }
     efc = (-1.602176487e-19 * -1.602176487e-19) / (4 * 3.1415926536 * 8.8541878176E-12 * 1e-2 * 1e-2 * 9.1093837015e-31);  // src/cell.cu:5
 
     if (device < 64) {
@@ -728,7 +740,7 @@ int Sim::init_uniform(int init_n, unsigned long long id_base) {
 // ---- grid phase (src/pic.cu:501-504) ---------------------------------------------------------
 int Sim::op_deposit() {
     span_begin(kPhDeposit);
-    k_deposit<<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], cur, tables + kTableSmemBytes / 4);
+    k_deposit<<<deposit_blocks, 256, 0, stream>>>(soa, st, grid[cur], cur, tables + kTableSmemBytes / 4);
     charge_valid = true;
     ++launches;
     span_end();
@@ -746,8 +758,8 @@ int Sim::op_gather() {
     // dense plasma (decided on the device): the field once per cell of the occupied box, then one record per electron
     float4* const F = (cfg.nranks == 1 && field_launch) ? field : nullptr;
     if (F) { k_field_box<<<aux_blocks, 256, 0, stream>>>(st, grid[cur], F, efc, cur, field_ratio); ++launches; }
-    if (F) k_gather<true><<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, F, cur, field_ratio);
-    else k_gather<false><<<aux_blocks, 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, nullptr, cur, field_ratio);
+    if (F) k_gather<true><<<gather_blocks[1], 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, F, cur, field_ratio);
+    else k_gather<false><<<gather_blocks[0], 256, 0, stream>>>(soa, st, grid[cur], efc, tables + kTableSmemBytes / 4, nullptr, cur, field_ratio);
     ++launches;
     span_end();
     CK_LAST("Gather");
