@@ -105,3 +105,17 @@ def test_cli_usage_without_gpu(engine):
     # unknown mode string: runs nothing, still prints the CPU time (src/main.cu:26-46)
     r = subprocess.run([engine.CLI_PATH, "99", "0", "10", "1", "256", "100", "100", "10"], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.startswith("CPU time of program: ")
+
+
+def test_sass_budget_tool_follows_the_source(engine):
+    """tools/sass_budget.py finds the step loop of the fused kernel by marker text in csrc/pic_mover.cuh; an edit of the
+    loop that moves a marker must show up here, not as a silently dead tool (no GPU needed: SASS of the built library)."""
+    import shutil
+    import sys
+    if not (shutil.which("cuobjdump") and shutil.which("nvdisasm")):
+        pytest.skip("CUDA binary utilities not on PATH")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sass_budget.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
+    assert "step loop at items" in r.stdout and "philox" in r.stdout
+    m = re.search(r"(\d+) outside the spawn path", r.stdout)
+    assert m and 100 <= int(m.group(1)) <= 260, r.stdout[:600]      # (the hot part of a mobility step: ~150 instructions)
